@@ -1,0 +1,691 @@
+// capi.cu -- extern "C" layer of the B200 depth pipeline (see include/mvs_capi.h).
+//
+// Owns contexts (device + stream + optional NCCL communicator) and frames (device-resident
+// buffers of all views).  Host-side scalar preparation follows the reference:
+// clSLIC.cpp:15-23 (SLIC normalisers), pipeline.cpp:121-142 (levels, neighbour lists),
+// pipeline.cpp:164-166 + depth_refinement.cpp:130, 335-339, 734-738, 768-769 (refinement
+// parameters, per-iteration arguments), depth_refinement.cpp:744-753, 1352 (ping-pong and
+// the buffer fusion reads).
+#include "../../include/mvs_capi.h"
+#include "common.cuh"
+#include <nccl.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+
+using namespace mvs;
+
+static thread_local std::string g_err;
+
+static int fail(const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CK(call)                                                                                            \
+    do {                                                                                                    \
+        cudaError_t e_ = (call);                                                                            \
+        if (e_ != cudaSuccess) return fail("%s:%d CUDA error %d (%s) in %s", __FILE__, __LINE__, (int)e_,  \
+                                           cudaGetErrorString(e_), #call);                                  \
+    } while (0)
+#define NK(call)                                                                                            \
+    do {                                                                                                    \
+        ncclResult_t r_ = (call);                                                                           \
+        if (r_ != ncclSuccess) return fail("%s:%d NCCL error %d (%s) in %s", __FILE__, __LINE__, (int)r_,  \
+                                           ncclGetErrorString(r_), #call);                                  \
+    } while (0)
+
+struct mvs_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    long long launches = 0;
+    ncclComm_t comm = nullptr;
+    int nranks = 1, rank = 0;
+};
+
+enum { ST_SLIC = 0, ST_BOUNDARY, ST_BM, ST_FLAT, ST_INIT, ST_PROP, ST_FUSION, ST_EXCH, ST_COUNT };
+
+struct mvs_frame {
+    mvs_ctx *ctx = nullptr;
+    mvs_params p{};
+    FrameDev d{};
+    int lo = 0, hi = 0;
+    std::vector<int> h_subset, h_subset_num;
+    std::vector<float> h_levels;
+    // refinement scalars (set by prepare_refine)
+    float gamma_flat = 0, gamma = 0, alpha = 0, fuse = 0, kss = 0;
+    int kernel_step = 0, no_prop = 0;
+    float bl_ratio = 0;
+    float stage_ms[ST_COUNT] = {0};
+    std::vector<cudaEvent_t> ev;   // pairs (start, stop) tagged with a stage
+    std::vector<int> ev_stage;
+    size_t ev_used = 0;
+    bool timing = true;
+};
+
+extern "C" const char *mvs_last_error(void) { return g_err.c_str(); }
+
+extern "C" int mvs_device_count(int *count)
+{
+    CK(cudaGetDeviceCount(count));
+    return 0;
+}
+
+extern "C" int mvs_ctx_create(int device, mvs_ctx **out)
+{
+    if (!out) return fail("mvs_ctx_create: null out");
+    int n = 0;
+    CK(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail("mvs_ctx_create: device %d out of range (%d CUDA devices)", device, n);
+    CK(cudaSetDevice(device));
+    mvs_ctx *c = new mvs_ctx;
+    c->device = device;
+    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete c; return fail("cudaStreamCreate: %s", cudaGetErrorString(e)); }
+    *out = c;
+    return 0;
+}
+
+extern "C" int mvs_ctx_destroy(mvs_ctx *c)
+{
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    if (c->comm) ncclCommDestroy(c->comm);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return 0;
+}
+
+extern "C" int mvs_ctx_sync(mvs_ctx *c)
+{
+    if (!c) return fail("null ctx");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+extern "C" int mvs_ctx_launch_count(mvs_ctx *c, long long *count)
+{
+    if (!c || !count) return fail("null argument");
+    *count = c->launches;
+    return 0;
+}
+
+extern "C" int mvs_ctx_stream(mvs_ctx *c, void **stream)
+{
+    if (!c || !stream) return fail("null argument");
+    *stream = (void *)c->stream;
+    return 0;
+}
+
+extern "C" int mvs_comm_unique_id(void *id128)
+{
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    NK(ncclGetUniqueId((ncclUniqueId *)id128));
+    return 0;
+}
+
+extern "C" int mvs_comm_init(mvs_ctx *c, const void *id128, int nranks, int rank)
+{
+    if (!c) return fail("null ctx");
+    CK(cudaSetDevice(c->device));
+    ncclUniqueId id;
+    memcpy(&id, id128, sizeof id);
+    NK(ncclCommInitRank(&c->comm, nranks, id, rank));
+    c->nranks = nranks;
+    c->rank = rank;
+    return 0;
+}
+
+extern "C" int mvs_host_alloc(void **p, size_t bytes)
+{
+    CK(cudaHostAlloc(p, bytes, cudaHostAllocDefault));
+    return 0;
+}
+
+extern "C" int mvs_host_free(void *p)
+{
+    CK(cudaFreeHost(p));
+    return 0;
+}
+
+// contiguous partition of V views over n ranks (first V%n ranks get one more)
+extern "C" int mvs_view_partition(int V, int nranks, int rank, int *lo, int *hi)
+{
+    if (nranks <= 0 || rank < 0 || rank >= nranks) return fail("bad rank %d/%d", rank, nranks);
+    int base = V / nranks, rem = V % nranks;
+    int l = rank * base + std::min(rank, rem);
+    *lo = l;
+    *hi = l + base + (rank < rem ? 1 : 0);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// frame
+// ---------------------------------------------------------------------------------------
+static size_t elem_bytes(const mvs_frame *f, int which, bool *per_pixel)
+{
+    switch (which) {
+    case MVS_BUF_RGBX: *per_pixel = true; return 4;
+    case MVS_BUF_LAB: *per_pixel = true; return 16;
+    case MVS_BUF_IDX: *per_pixel = true; return 4;
+    case MVS_BUF_DISP: *per_pixel = true; return 4;
+    case MVS_BUF_MAP: *per_pixel = false; return 32;
+    case MVS_BUF_REP: *per_pixel = false; return 8;
+    case MVS_BUF_FLAT: *per_pixel = false; return 8;
+    case MVS_BUF_STATE_A:
+    case MVS_BUF_STATE_B: *per_pixel = false; return 24;
+    }
+    *per_pixel = false;
+    return 0;
+}
+
+static void *buf_ptr(mvs_frame *f, int which)
+{
+    switch (which) {
+    case MVS_BUF_RGBX: return f->d.rgbx;
+    case MVS_BUF_LAB: return f->d.lab;
+    case MVS_BUF_IDX: return f->d.idx;
+    case MVS_BUF_DISP: return f->d.disp;
+    case MVS_BUF_MAP: return f->d.map;
+    case MVS_BUF_REP: return f->d.rep;
+    case MVS_BUF_FLAT: return f->d.flat;
+    case MVS_BUF_STATE_A: return f->d.state6[0];
+    case MVS_BUF_STATE_B: return f->d.state6[1];
+    }
+    return nullptr;
+}
+
+static int set_tables(mvs_frame *f, const int *subset, const int *subset_num, const float *levels, int nlev)
+{
+    int V = f->d.V;
+    f->h_subset.assign(subset, subset + (size_t)V * V);
+    f->h_subset_num.assign(subset_num, subset_num + V);
+    for (int z = 0; z < V; ++z) {
+        if (subset_num[z] < 0 || subset_num[z] > V) return fail("subset_num[%d]=%d out of range", z, subset_num[z]);
+        for (int k = 0; k < subset_num[z]; ++k)
+            if (subset[z * V + k] < 0 || subset[z * V + k] >= V) return fail("view_subset[%d][%d] out of range", z, k);
+    }
+    cudaStream_t st = f->ctx->stream;
+    CK(cudaMemcpyAsync(f->d.view_subset, f->h_subset.data(), sizeof(int) * V * V, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(f->d.subset_num, f->h_subset_num.data(), sizeof(int) * V, cudaMemcpyHostToDevice, st));
+    if (levels) {
+        if (f->d.levels) CK(cudaFree(f->d.levels));
+        f->h_levels.assign(levels, levels + nlev);
+        CK(cudaMalloc(&f->d.levels, sizeof(float) * std::max(nlev, 1)));
+        CK(cudaMemcpyAsync(f->d.levels, f->h_levels.data(), sizeof(float) * nlev, cudaMemcpyHostToDevice, st));
+        f->d.num_levels = nlev;
+    }
+    CK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// refinement scalars from the values pipeline::refine_depth_map passes (gamma_ = 2g^2 ...)
+static void prepare_refine(mvs_frame *f, float gamma_, float alpha_, float fuse_, int kernel_step, int kernel_size,
+                           int no_prop, float bl_ratio)
+{
+    f->gamma_flat = (float)(1.0 / (double)gamma_);                                  // depth_refinement.cpp:130
+    f->gamma = 1 / gamma_;                                                           // :335
+    f->alpha = 1 / alpha_;                                                           // :336
+    f->kss = (float)std::max(1, kernel_size / kernel_step * f->d.S);                 // :338 (int math)
+    f->fuse = (float)(0.5 * fuse_);                                                  // :339
+    f->kernel_step = kernel_step;
+    f->no_prop = no_prop;
+    f->bl_ratio = bl_ratio;
+}
+
+extern "C" int mvs_frame_destroy(mvs_frame *f)
+{
+    if (!f) return 0;
+    cudaSetDevice(f->ctx->device);
+    cudaStreamSynchronize(f->ctx->stream);
+    FrameDev &d = f->d;
+    cudaFree(d.rgbx); cudaFree(d.lab); cudaFree(d.idx); cudaFree(d.idx_tmp); cudaFree(d.map); cudaFree(d.rep);
+    cudaFree(d.flat); cudaFree(d.disp); cudaFree(d.view_subset); cudaFree(d.subset_num); cudaFree(d.levels);
+    for (int k = 0; k < 2; ++k) { cudaFree(d.plane[k]); cudaFree(d.cost[k]); cudaFree(d.state6[k]); }
+    for (cudaEvent_t e : f->ev) cudaEventDestroy(e);
+    delete f;
+    return 0;
+}
+
+static int frame_alloc(mvs_ctx *ctx, int W, int H, int S, int aw, int ah, bool need_rgbx, bool need_lab, bool need_disp,
+                       bool need_tmp, mvs_frame **out)
+{
+    if (!ctx || !out) return fail("null argument");
+    if (W <= 0 || H <= 0 || aw <= 0 || ah <= 0) return fail("bad geometry %dx%d array %dx%d", W, H, aw, ah);
+    if (S < 6) return fail("spixl_size %d < 6 is not supported (cluster_per_line = 3S/16 would be 0, clSLIC.cpp:313)", S);
+    if (W < S || H < S) return fail("image %dx%d smaller than one superpixel (%d)", W, H, S);
+    CK(cudaSetDevice(ctx->device));
+    mvs_frame *f = new mvs_frame;
+    f->ctx = ctx;
+    FrameDev &d = f->d;
+    d.V = aw * ah; d.W = W; d.H = H; d.S = S; d.aw = aw; d.ah = ah;
+    d.mw = (int)ceilf((float)W / (float)S);   // pipeline.cpp:18-19
+    d.mh = (int)ceilf((float)H / (float)S);
+    d.N = W * H; d.M = d.mw * d.mh;
+    if ((double)d.M >= 16777216.0) { delete f; return fail("more than 2^24 superpixels per view"); }
+    size_t VN = (size_t)d.V * d.N, VM = (size_t)d.V * d.M;
+    cudaError_t e = cudaSuccess;
+    auto A = [&](void **p, size_t bytes) { if (e == cudaSuccess) { e = cudaMalloc(p, bytes); if (e == cudaSuccess) e = cudaMemsetAsync(*p, 0, bytes, ctx->stream); } };
+    if (need_rgbx) A((void **)&d.rgbx, VN * 4);
+    if (need_lab) A((void **)&d.lab, VN * 16);
+    A((void **)&d.idx, VN * 4);
+    if (need_tmp) A((void **)&d.idx_tmp, VN * 4);
+    A((void **)&d.map, VM * 32);
+    A((void **)&d.rep, VM * 8);
+    A((void **)&d.flat, VM * 8);
+    for (int k = 0; k < 2; ++k) { A((void **)&d.plane[k], VM * 16); A((void **)&d.cost[k], VM * 8); A((void **)&d.state6[k], VM * 24); }
+    if (need_disp) A((void **)&d.disp, VN * 4);
+    A((void **)&d.view_subset, sizeof(int) * d.V * d.V);
+    A((void **)&d.subset_num, sizeof(int) * d.V);
+    if (e != cudaSuccess) { mvs_frame_destroy(f); return fail("frame allocation failed: %s", cudaGetErrorString(e)); }
+    f->lo = 0; f->hi = d.V;
+    *out = f;
+    return 0;
+}
+
+extern "C" int mvs_frame_create(mvs_ctx *ctx, const mvs_params *p, int view_lo, int view_hi, mvs_frame **out)
+{
+    if (!p) return fail("null params");
+    int V = p->array_width * p->array_height;
+    if (view_lo < 0 || view_hi > V || view_lo > view_hi) return fail("bad view range [%d,%d) of %d", view_lo, view_hi, V);
+    if (p->inc <= 0 || p->max_disp < p->min_disp) return fail("bad disparity range");
+    if (p->kernel_step <= 0) return fail("kernel_step must be positive");
+    mvs_frame *f = nullptr;
+    if (frame_alloc(ctx, p->width, p->height, p->spixl_size, p->array_width, p->array_height, true, true, true,
+                    p->enforce_connectivity != 0, &f))
+        return 1;
+    f->p = *p;
+    f->lo = view_lo; f->hi = view_hi;
+    // disparity levels and neighbour lists, pipeline.cpp:121-142 (x outer, y inner, self excluded)
+    std::vector<float> lev;
+    for (int i = 0; i <= (p->max_disp - p->min_disp) / p->inc; i++) lev.push_back((float)(p->min_disp + i * p->inc));
+    std::vector<int> sub((size_t)V * V, 0), num(V, 0);
+    int aw = p->array_width, ah = p->array_height;
+    for (int i = 0; i < V; i++)
+        for (int x = i % aw - p->neib_hor; x <= i % aw + p->neib_hor; x++)
+            for (int y = i / aw - p->neib_ver; y <= i / aw + p->neib_ver; y++) {
+                int indx = y * aw + x;
+                if (x >= 0 && x < aw && y >= 0 && y < ah && indx != i) sub[(size_t)i * V + num[i]++] = indx;
+            }
+    if (set_tables(f, sub.data(), num.data(), lev.data(), (int)lev.size())) { mvs_frame_destroy(f); return 1; }
+    float g = (float)(2 * pow((double)p->gamma, 2)), a = (float)(2 * pow((double)p->alpha, 2));   // pipeline.cpp:164-165
+    prepare_refine(f, g, a, p->fuse, p->kernel_step, p->kernel_size / 2, p->no_prop, p->bl_ratio);
+    *out = f;
+    return 0;
+}
+
+extern "C" int mvs_frame_sizes(mvs_frame *f, int *V, int *W, int *H, int *mw, int *mh, int *num_levels)
+{
+    if (!f) return fail("null frame");
+    if (V) *V = f->d.V;
+    if (W) *W = f->d.W;
+    if (H) *H = f->d.H;
+    if (mw) *mw = f->d.mw;
+    if (mh) *mh = f->d.mh;
+    if (num_levels) *num_levels = f->d.num_levels;
+    return 0;
+}
+
+extern "C" int mvs_frame_dev_ptr(mvs_frame *f, int which, void **dev)
+{
+    if (!f || !dev) return fail("null argument");
+    void *p = buf_ptr(f, which);
+    if (!p) return fail("buffer %d not allocated", which);
+    *dev = p;
+    return 0;
+}
+
+static int xfer(mvs_frame *f, int which, int v0, int v1, void *host, bool up, bool sync)
+{
+    if (!f || !host) return fail("null argument");
+    if (v0 < 0 || v1 > f->d.V || v0 > v1) return fail("bad view range [%d,%d)", v0, v1);
+    bool pp;
+    size_t eb = elem_bytes(f, which, &pp);
+    char *dev = (char *)buf_ptr(f, which);
+    if (!eb || !dev) return fail("buffer %d not available", which);
+    CK(cudaSetDevice(f->ctx->device));
+    size_t per_view = eb * (pp ? (size_t)f->d.N : (size_t)f->d.M);
+    cudaStream_t st = f->ctx->stream;
+    bool state = which == MVS_BUF_STATE_A || which == MVS_BUF_STATE_B;
+    int w = which == MVS_BUF_STATE_B ? 1 : 0;
+    if (!up && state) f->ctx->launches += launch_export_state(f->d, w, v0, v1, st);
+    if (up) CK(cudaMemcpyAsync(dev + per_view * v0, host, per_view * (v1 - v0), cudaMemcpyHostToDevice, st));
+    else CK(cudaMemcpyAsync(host, dev + per_view * v0, per_view * (v1 - v0), cudaMemcpyDeviceToHost, st));
+    if (up && state) f->ctx->launches += launch_import_state(f->d, w, v0, v1, st);
+    if (sync) CK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" int mvs_frame_upload(mvs_frame *f, int which, int v0, int v1, const void *host)
+{
+    return xfer(f, which, v0, v1, (void *)host, true, true);
+}
+extern "C" int mvs_frame_download(mvs_frame *f, int which, int v0, int v1, void *host)
+{
+    return xfer(f, which, v0, v1, host, false, true);
+}
+// asynchronous variants on the context stream (host memory should be pinned)
+extern "C" int mvs_frame_upload_async(mvs_frame *f, int which, int v0, int v1, const void *host)
+{
+    return xfer(f, which, v0, v1, (void *)host, true, false);
+}
+extern "C" int mvs_frame_download_async(mvs_frame *f, int which, int v0, int v1, void *host)
+{
+    return xfer(f, which, v0, v1, host, false, false);
+}
+
+// ---- stage timing -----------------------------------------------------------------------
+struct StageTimer {
+    mvs_frame *f;
+    bool on;
+    StageTimer(mvs_frame *f_, int stage) : f(f_), on(f_->timing)
+    {
+        if (!on) return;
+        if (f->ev_used + 2 > f->ev.size()) {
+            cudaEvent_t a, b;
+            cudaEventCreate(&a); cudaEventCreate(&b);
+            f->ev.push_back(a); f->ev.push_back(b);
+            f->ev_stage.push_back(stage); f->ev_stage.push_back(stage);
+        }
+        f->ev_stage[f->ev_used] = stage;
+        cudaEventRecord(f->ev[f->ev_used], f->ctx->stream);
+    }
+    ~StageTimer()
+    {
+        if (!on) return;
+        cudaEventRecord(f->ev[f->ev_used + 1], f->ctx->stream);
+        f->ev_used += 2;
+    }
+};
+
+extern "C" int mvs_frame_set_timing(mvs_frame *f, int enable)
+{
+    if (!f) return fail("null frame");
+    f->timing = enable != 0;
+    return 0;
+}
+
+extern "C" int mvs_frame_stage_ms(mvs_frame *f, float *ms8)
+{
+    if (!f || !ms8) return fail("null argument");
+    CK(cudaSetDevice(f->ctx->device));
+    CK(cudaStreamSynchronize(f->ctx->stream));
+    for (int k = 0; k < ST_COUNT; ++k) f->stage_ms[k] = 0;
+    for (size_t i = 0; i + 1 < f->ev_used; i += 2) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, f->ev[i], f->ev[i + 1]));
+        f->stage_ms[f->ev_stage[i]] += ms;
+    }
+    f->ev_used = 0;
+    memcpy(ms8, f->stage_ms, sizeof(float) * ST_COUNT);
+    return 0;
+}
+
+static int check_launch(const char *what)
+{
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail("%s: kernel launch failed: %s", what, cudaGetErrorString(e));
+    return 0;
+}
+
+// ---- multi-GPU halo exchange ---------------------------------------------------------------
+// Rank r needs view v when v is a neighbour (view_subset) of one of r's own views.  Every
+// rank derives the same global plan; transfers are grouped ncclSend/ncclRecv over NVLink.
+static int exchange_raw(mvs_frame *f, char *base, size_t per_view)
+{
+    mvs_ctx *c = f->ctx;
+    if (!c->comm || c->nranks == 1) return 0;
+    int V = f->d.V, n = c->nranks;
+    std::vector<int> lo(n), hi(n), owner(V);
+    for (int r = 0; r < n; ++r) {
+        mvs_view_partition(V, n, r, &lo[r], &hi[r]);
+        for (int v = lo[r]; v < hi[r]; ++v) owner[v] = r;
+    }
+    NK(ncclGroupStart());
+    for (int r = 0; r < n; ++r) {
+        std::vector<char> need(V, 0);
+        for (int u = lo[r]; u < hi[r]; ++u)
+            for (int k = 0; k < f->h_subset_num[u]; ++k) need[f->h_subset[(size_t)u * V + k]] = 1;
+        for (int v = 0; v < V; ++v) {
+            if (!need[v] || owner[v] == r) continue;
+            if (owner[v] == c->rank) NK(ncclSend(base + per_view * v, per_view, ncclChar, r, c->comm, c->stream));
+            if (r == c->rank) NK(ncclRecv(base + per_view * v, per_view, ncclChar, owner[v], c->comm, c->stream));
+        }
+    }
+    NK(ncclGroupEnd());
+    return 0;
+}
+
+// views this rank reads but does not own
+static void halo_views(mvs_frame *f, std::vector<int> &out)
+{
+    int V = f->d.V;
+    std::vector<char> need(V, 0);
+    for (int u = f->lo; u < f->hi; ++u)
+        for (int k = 0; k < f->h_subset_num[u]; ++k) need[f->h_subset[(size_t)u * V + k]] = 1;
+    for (int v = 0; v < V; ++v)
+        if (need[v] && (v < f->lo || v >= f->hi)) out.push_back(v);
+}
+
+extern "C" int mvs_frame_exchange(mvs_frame *f, int which)
+{
+    if (!f) return fail("null frame");
+    CK(cudaSetDevice(f->ctx->device));
+    StageTimer t(f, ST_EXCH);
+    bool pp;
+    size_t eb;
+    char *base;
+    if (which == MVS_BUF_STATE_A || which == MVS_BUF_STATE_B) {   // internal plane array, 16 B / superpixel
+        base = (char *)f->d.plane[which == MVS_BUF_STATE_B];
+        eb = 16; pp = false;
+    } else {
+        eb = elem_bytes(f, which, &pp);
+        base = (char *)buf_ptr(f, which);
+    }
+    if (!eb || !base) return fail("buffer %d not available", which);
+    return exchange_raw(f, base, eb * (pp ? (size_t)f->d.N : (size_t)f->d.M));
+}
+
+// ---- stages --------------------------------------------------------------------------------
+extern "C" int mvs_frame_slic(mvs_frame *f)
+{
+    if (!f) return fail("null frame");
+    if (!f->d.rgbx || !f->d.lab) return fail("frame has no image buffers");
+    CK(cudaSetDevice(f->ctx->device));
+    StageTimer t(f, ST_SLIC);
+    cudaStream_t st = f->ctx->stream;
+    int S = f->d.S;
+    SlicArgs a;
+    a.max_xy_dist = 1.0f / (1.4242f * S);        // clSLIC.cpp:15-18
+    a.max_color_dist = 15.0f / (1.7321f * 128);
+    a.max_xy_dist *= a.max_xy_dist;
+    a.max_color_dist *= a.max_color_dist;
+    a.weight = f->p.slic_color_weight;
+    long long &L = f->ctx->launches;
+    L += launch_cvt(f->d, f->lo, f->hi, st);
+    L += launch_init_centers(f->d, f->lo, f->hi, st);
+    L += launch_assoc(f->d, a, f->lo, f->hi, st);
+    for (int i = 0; i < f->p.no_iter; ++i) {
+        L += launch_update_centers(f->d, f->lo, f->hi, st);
+        L += launch_assoc(f->d, a, f->lo, f->hi, st);
+    }
+    if (f->p.enforce_connectivity) {
+        if (!f->d.idx_tmp) return fail("connectivity buffer not allocated");
+        L += launch_connectivity(f->d, f->lo, f->hi, st);
+    }
+    return check_launch("slic");
+}
+
+// after SLIC on a sharded frame: ship RGBX (4 B/px) + labels + centres of the halo views and
+// recompute their Lab locally (bit-identical by construction, 4x less traffic than Lab)
+static int exchange_after_slic(mvs_frame *f)
+{
+    if (!f->ctx->comm || f->ctx->nranks == 1) return 0;
+    if (mvs_frame_exchange(f, MVS_BUF_RGBX) || mvs_frame_exchange(f, MVS_BUF_IDX) || mvs_frame_exchange(f, MVS_BUF_MAP))
+        return 1;
+    std::vector<int> halo;
+    halo_views(f, halo);
+    StageTimer t(f, ST_EXCH);
+    for (int v : halo) f->ctx->launches += launch_cvt(f->d, v, v + 1, f->ctx->stream);
+    return check_launch("halo cvt");
+}
+
+extern "C" int mvs_frame_block_match(mvs_frame *f)
+{
+    if (!f) return fail("null frame");
+    if (!f->d.lab || !f->d.levels) return fail("frame has no Lab / level buffers");
+    CK(cudaSetDevice(f->ctx->device));
+    cudaStream_t st = f->ctx->stream;
+    {
+        StageTimer t(f, ST_BOUNDARY);
+        f->ctx->launches += launch_boundary(f->d, f->lo, f->hi, st);
+    }
+    {
+        StageTimer t(f, ST_BM);
+        f->ctx->launches += launch_block_match(f->d, f->bl_ratio, f->lo, f->hi, st);
+    }
+    return check_launch("block_match");
+}
+
+extern "C" int mvs_frame_flatness(mvs_frame *f)
+{
+    if (!f) return fail("null frame");
+    CK(cudaSetDevice(f->ctx->device));
+    StageTimer t(f, ST_FLAT);
+    f->ctx->launches += launch_flatness(f->d, f->gamma_flat, f->lo, f->hi, f->ctx->stream);
+    return check_launch("flatness");
+}
+
+extern "C" int mvs_frame_init_state(mvs_frame *f)
+{
+    if (!f) return fail("null frame");
+    CK(cudaSetDevice(f->ctx->device));
+    StageTimer t(f, ST_INIT);
+    RefineArgs a{f->gamma, f->alpha, f->fuse, f->bl_ratio, f->kernel_step, f->kss, 0};
+    f->ctx->launches += launch_init_state(f->d, a, f->lo, f->hi, f->ctx->stream);
+    return check_launch("init_state");
+}
+
+extern "C" int mvs_frame_propagate(mvs_frame *f, int iter)
+{
+    if (!f) return fail("null frame");
+    if (iter < 0) return fail("negative iteration");
+    CK(cudaSetDevice(f->ctx->device));
+    int src = iter & 1, dst = src ^ 1;   // even: A -> B, odd: B -> A (depth_refinement.cpp:744-753)
+    if (f->ctx->comm && f->ctx->nranks > 1)
+        if (mvs_frame_exchange(f, src ? MVS_BUF_STATE_B : MVS_BUF_STATE_A)) return 1;
+    StageTimer t(f, ST_PROP);
+    // per-iteration arguments, depth_refinement.cpp:768-769 (int / int, float / int)
+    RefineArgs a{f->gamma, f->alpha, f->fuse, f->bl_ratio, f->kernel_step / (iter + 1), f->kss / (float)(iter + 1), iter};
+    f->ctx->launches += launch_propagate(f->d, a, src, dst, f->lo, f->hi, f->ctx->stream);
+    return check_launch("propagate");
+}
+
+extern "C" int mvs_frame_fusion(mvs_frame *f)
+{
+    if (!f) return fail("null frame");
+    if (!f->d.disp) return fail("frame has no disparity buffer");
+    CK(cudaSetDevice(f->ctx->device));
+    StageTimer t(f, ST_FUSION);
+    // fusion always reads buffer A (depth_refinement.cpp:1352)
+    f->ctx->launches += launch_spixl_to_image(f->d, 0, f->lo, f->hi, f->ctx->stream);
+    return check_launch("fusion");
+}
+
+extern "C" int mvs_frame_refine(mvs_frame *f)
+{
+    if (mvs_frame_flatness(f) || mvs_frame_init_state(f)) return 1;
+    for (int i = 0; i < f->no_prop; ++i)
+        if (mvs_frame_propagate(f, i)) return 1;
+    return mvs_frame_fusion(f);
+}
+
+extern "C" int mvs_frame_run(mvs_frame *f)
+{
+    if (mvs_frame_slic(f)) return 1;
+    if (exchange_after_slic(f)) return 1;
+    if (mvs_frame_block_match(f)) return 1;
+    if (f->ctx->comm && f->ctx->nranks > 1)
+        if (mvs_frame_exchange(f, MVS_BUF_MAP)) return 1;
+    return mvs_frame_refine(f);
+}
+
+// ---------------------------------------------------------------------------------------
+// class-level entry points (host pointers, reference semantics)
+// ---------------------------------------------------------------------------------------
+extern "C" int mvs_slic_run(mvs_ctx *ctx, int width, int height, int spixl_size, float color_weight, int no_iter,
+                            int enforce_connectivity, int count, const void *rgbx, void *lab, void *map, uint32_t *idx)
+{
+    if (!rgbx) return fail("null input image");
+    if (count <= 0) return fail("count must be positive");
+    mvs_frame *f = nullptr;
+    // `count` independent images = a count x 1 "array" with no neighbour relations
+    if (frame_alloc(ctx, width, height, spixl_size, count, 1, true, true, false, enforce_connectivity != 0, &f)) return 1;
+    f->p.slic_color_weight = color_weight;
+    f->p.no_iter = no_iter;
+    f->p.enforce_connectivity = enforce_connectivity;
+    f->timing = false;
+    int rc = mvs_frame_upload_async(f, MVS_BUF_RGBX, 0, count, rgbx) || mvs_frame_slic(f) ||
+             (lab && mvs_frame_download_async(f, MVS_BUF_LAB, 0, count, lab)) ||
+             (map && mvs_frame_download_async(f, MVS_BUF_MAP, 0, count, map)) ||
+             (idx && mvs_frame_download_async(f, MVS_BUF_IDX, 0, count, idx)) || mvs_ctx_sync(ctx);
+    mvs_frame_destroy(f);
+    return rc;
+}
+
+extern "C" int mvs_bm_run(mvs_ctx *ctx, int view_count, int width, int height, int spixl_size, float *map, uint8_t *rep,
+                          const float *lab, const uint32_t *idx, int array_width, float bl_ratio, const int *view_subset,
+                          const int *subset_num, const float *disp_levels, int num_levels)
+{
+    if (!map || !rep || !lab || !idx || !view_subset || !subset_num || !disp_levels) return fail("null argument");
+    if (array_width <= 0 || view_count <= 0) return fail("bad view geometry");
+    mvs_frame *f = nullptr;
+    // the kernels only use array_width (view -> grid position); rows follow from the view count
+    int ah = (view_count + array_width - 1) / array_width;
+    if (ah * array_width != view_count) return fail("view_count %d is not a multiple of array_width %d", view_count, array_width);
+    if (frame_alloc(ctx, width, height, spixl_size, array_width, ah, false, true, false, false, &f)) return 1;
+    f->timing = false;
+    f->bl_ratio = bl_ratio;
+    int V = view_count;
+    int rc = set_tables(f, view_subset, subset_num, disp_levels, num_levels) ||
+             mvs_frame_upload_async(f, MVS_BUF_LAB, 0, V, lab) || mvs_frame_upload_async(f, MVS_BUF_IDX, 0, V, idx) ||
+             mvs_frame_upload_async(f, MVS_BUF_MAP, 0, V, map) || mvs_frame_block_match(f) ||
+             mvs_frame_download_async(f, MVS_BUF_REP, 0, V, rep) || mvs_frame_download_async(f, MVS_BUF_MAP, 0, V, map) ||
+             mvs_ctx_sync(ctx);
+    mvs_frame_destroy(f);
+    return rc;
+}
+
+extern "C" int mvs_refine_run(mvs_ctx *ctx, int width, int height, int array_width, int array_height, int spixl_size,
+                              float bl_ratio, const float *map, const uint32_t *idx, const uint8_t *rep,
+                              const int *view_subset, const int *subset_num, float gamma, float alpha, float fuse,
+                              int kernel_step, int kernel_size, int no_prop, float *flat, float *state_a, float *state_b,
+                              float *disp)
+{
+    if (!map || !idx || !rep || !view_subset || !subset_num) return fail("null argument");
+    if (kernel_step <= 0) return fail("kernel_step must be positive");
+    mvs_frame *f = nullptr;
+    if (frame_alloc(ctx, width, height, spixl_size, array_width, array_height, false, false, true, false, &f)) return 1;
+    f->timing = false;
+    int V = f->d.V;
+    prepare_refine(f, gamma, alpha, fuse, kernel_step, kernel_size, no_prop, bl_ratio);
+    int rc = set_tables(f, view_subset, subset_num, nullptr, 0) || mvs_frame_upload_async(f, MVS_BUF_MAP, 0, V, map) ||
+             mvs_frame_upload_async(f, MVS_BUF_IDX, 0, V, idx) || mvs_frame_upload_async(f, MVS_BUF_REP, 0, V, rep) ||
+             mvs_frame_refine(f) || (flat && mvs_frame_download_async(f, MVS_BUF_FLAT, 0, V, flat)) ||
+             (state_a && mvs_frame_download_async(f, MVS_BUF_STATE_A, 0, V, state_a)) ||
+             (state_b && mvs_frame_download_async(f, MVS_BUF_STATE_B, 0, V, state_b)) ||
+             (disp && mvs_frame_download_async(f, MVS_BUF_DISP, 0, V, disp)) || mvs_ctx_sync(ctx);
+    mvs_frame_destroy(f);
+    return rc;
+}

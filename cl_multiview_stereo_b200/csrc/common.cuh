@@ -1,0 +1,59 @@
+// common.cuh -- shared declarations of the sm_100a depth-pipeline library.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mvs {
+
+// Geometry + device pointers of one frame (all V views; view-major arrays).
+struct FrameDev {
+    int V, W, H, mw, mh, S, aw, ah;
+    int N;              // W*H
+    int M;              // mw*mh
+    uchar4 *rgbx;       // [V][N]
+    float4 *lab;        // [V][N]   {L,a,b,0}
+    uint32_t *idx;      // [V][N]
+    uint32_t *idx_tmp;  // [V][N]   connectivity ping-pong (allocated on demand)
+    float4 *map;        // [V][M][2] float8 {id,cx,cy,L | a,b,n,disp}
+    uint2 *rep;         // [V][M]   uchar8 packed little-endian {nw,w,sw,n | s,ne,e,se}
+    float2 *flat;       // [V][M]
+    float4 *plane[2];   // [V][M]   {d,nx,ny,nz}  internal SoA split of the 6-float state (A,B)
+    float2 *cost[2];    // [V][M]   {sm,cs}
+    float *state6[2];   // [V][M][6] API layout, filled on export
+    float *disp;        // [V][N]
+    int *view_subset;   // [V][V]
+    int *subset_num;    // [V]
+    float *levels;      // [L]
+    int num_levels;
+};
+
+struct SlicArgs {
+    float max_xy_dist, max_color_dist, weight;
+};
+
+struct RefineArgs {
+    float gamma, alpha, fuse, bl_ratio;
+    int no_kernel_steps;
+    float kernel_step_size;
+    int iter;
+};
+
+// launchers (all asynchronous on `st`); z0..z1-1 = views to compute.  Each returns the
+// number of kernel launches it issued.
+int launch_cvt(const FrameDev &f, int z0, int z1, cudaStream_t st);
+int launch_init_centers(const FrameDev &f, int z0, int z1, cudaStream_t st);
+int launch_assoc(const FrameDev &f, const SlicArgs &a, int z0, int z1, cudaStream_t st);
+int launch_update_centers(const FrameDev &f, int z0, int z1, cudaStream_t st);
+int launch_connectivity(const FrameDev &f, int z0, int z1, cudaStream_t st);
+
+int launch_boundary(const FrameDev &f, int z0, int z1, cudaStream_t st);
+int launch_block_match(const FrameDev &f, float bl_ratio, int z0, int z1, cudaStream_t st);
+
+int launch_flatness(const FrameDev &f, float gamma_flat, int z0, int z1, cudaStream_t st);
+int launch_init_state(const FrameDev &f, const RefineArgs &a, int z0, int z1, cudaStream_t st);
+int launch_propagate(const FrameDev &f, const RefineArgs &a, int src, int dst, int z0, int z1, cudaStream_t st);
+int launch_spixl_to_image(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);
+int launch_export_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
+int launch_import_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
+
+} // namespace mvs

@@ -1,0 +1,311 @@
+// slic.cu -- superpixel segmentation kernels (sm_100a).
+//
+// Replaces the OpenCL kernels driven by clSLIC::do_super_pixel_seg
+// (reference clMVDE/clSLIC.cpp:67-122): cvt (clcode.cl:125-151), init_cluster_centers
+// (:259-294), find_center_association (:447-520), update_cluster_center +
+// finalize_reduction_result (:533-611, :719-773), supress_local_lable (:676-711).
+// All views of a frame go through one launch (blockIdx.z / .y = view).
+#include "common.cuh"
+#include "mvs_math.cuh"
+
+namespace mvs {
+
+// ---------------------------------------------------------------------------------------
+// RGB -> CIELAB.  The loader stores s0=R,s1=G,s2=B (file_handler.cpp:11-13) while the
+// conversion reads s0 as blue and s2 as red (clcode.cl:25-27); kept as is.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float lab_f(float t)
+{
+    return t > 0.008856f ? cbrtf_pos(t) : (903.3f * t + 16.0f) / 116.0f;
+}
+
+__device__ __forceinline__ float4 rgb2lab(uchar4 p)
+{
+    float b = (float)p.x * 0.0039216f;
+    float g = (float)p.y * 0.0039216f;
+    float r = (float)p.z * 0.0039216f;
+    float x = r * 0.412453f + g * 0.357580f + b * 0.180423f;
+    float y = r * 0.212671f + g * 0.715160f + b * 0.072169f;
+    float z = r * 0.019334f + g * 0.119193f + b * 0.950227f;
+    float fx = lab_f(x / 0.950456f);
+    float fy = lab_f(y / 1.0f);
+    float fz = lab_f(z / 1.088754f);
+    return make_float4(116.0f * fy - 16.0f, 500.0f * (fx - fy), 200.0f * (fy - fz), 0.0f);
+}
+
+__global__ void __launch_bounds__(256) k_cvt(const uchar4 *__restrict__ rgbx, float4 *__restrict__ lab, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) lab[i] = rgb2lab(rgbx[i]);
+}
+
+int launch_cvt(const FrameDev &f, int z0, int z1, cudaStream_t st)
+{
+    size_t n = (size_t)(z1 - z0) * f.N;
+    if (!n) return 0;
+    k_cvt<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(f.rgbx + (size_t)z0 * f.N, f.lab + (size_t)z0 * f.N, n);
+    return 1;
+}
+
+// ---------------------------------------------------------------------------------------
+// Cluster-centre initialisation: cell midpoint, '>' edge test (clcode.cl:273-277).  The
+// reference can read one past the image when W mod S == S/2; the read is clamped here.
+// s7 (left unwritten by the reference) is set to 0.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_init_centers(const float4 *__restrict__ lab, float4 *__restrict__ map,
+                                                      int W, int H, int mw, int mh, int S, int N, int M, int z0)
+{
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    int z = z0 + blockIdx.y;
+    if (c >= M) return;
+    int col = c % mw, row = c / mw;
+    int cx = col * S + S / 2, cy = row * S + S / 2;
+    if (cx > W) cx = (col * S + W) / 2;
+    if (cy > H) cy = (row * S + H) / 2;
+    int rx = min(cx, W - 1), ry = min(cy, H - 1);
+    float4 p = lab[(size_t)z * N + (size_t)ry * W + rx];
+    float4 *m = map + 2 * ((size_t)z * M + c);
+    m[0] = make_float4((float)c, (float)cx, (float)cy, p.x);
+    m[1] = make_float4(p.y, p.z, 0.0f, 0.0f);
+}
+
+int launch_init_centers(const FrameDev &f, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    dim3 g((f.M + 255) / 256, z1 - z0);
+    k_init_centers<<<g, 256, 0, st>>>(f.lab, f.map, f.W, f.H, f.mw, f.mh, f.S, f.N, f.M, z0);
+    return 1;
+}
+
+// ---------------------------------------------------------------------------------------
+// Pixel -> centre association.  Live rule of the reference: 2x2 candidate cells chosen
+// by the half-cell phase, the outer loop variable (built from the x phase) offsets the
+// cell ROW and the inner one (y phase) the cell COLUMN (clcode.cl:475-479); strict '<'
+// so the first minimum wins; distance = sqrt(dc*Nc + w*(ds*Ns)) (clcode.cl:425-435).
+//
+// A CTA covers a TX x TY pixel tile; the (TX/S+2) x (TY/S+2) centres it can touch are
+// staged once in shared memory as {cx,cy,L,a,b}.
+// ---------------------------------------------------------------------------------------
+constexpr int AS_TX = 64, AS_TY = 8;   // tile in pixels (thread block = 64x8/ (4 px per thread in x))
+constexpr int AS_PX = 4;               // pixels per thread (one STG.128 of labels)
+
+template <int S_T>
+__global__ void __launch_bounds__(AS_TX / AS_PX * AS_TY)
+k_assoc(const float4 *__restrict__ lab, const float4 *__restrict__ map, uint32_t *__restrict__ idx, int W, int H,
+        int mw, int mh, int S_rt, int N, int M, int z0, float max_xy_dist, float max_color_dist, float weight)
+{
+    const int S = S_T > 0 ? S_T : S_rt;
+    extern __shared__ float s_ctr[];   // [cells][5]
+    int z = z0 + blockIdx.z;
+    int tx0 = blockIdx.x * AS_TX, ty0 = blockIdx.y * AS_TY;
+    // candidate cell range of the tile: cells (tx0/S - 1 .. (tx0+TX-1)/S + 1), same in y
+    int ccx0 = tx0 / S - 1, ccy0 = ty0 / S - 1;
+    int ncx = (tx0 + AS_TX - 1) / S + 1 - ccx0 + 1;
+    int ncy = (ty0 + AS_TY - 1) / S + 1 - ccy0 + 1;
+    const float4 *vmap = map + 2 * (size_t)z * M;
+    int tid = threadIdx.y * blockDim.x + threadIdx.x;
+    for (int k = tid; k < ncx * ncy; k += blockDim.x * blockDim.y) {
+        int gx = ccx0 + k % ncx, gy = ccy0 + k / ncx;
+        float4 a = make_float4(0, 0, 0, 0), b = make_float4(0, 0, 0, 0);
+        if (gx >= 0 && gy >= 0 && gx < mw && gy < mh) {
+            a = vmap[2 * (gy * mw + gx)];
+            b = vmap[2 * (gy * mw + gx) + 1];
+        }
+        float *s = s_ctr + 5 * k;
+        s[0] = a.y; s[1] = a.z; s[2] = a.w; s[3] = b.x; s[4] = b.y;
+    }
+    __syncthreads();
+
+    int row = ty0 + threadIdx.y;
+    int colb = tx0 + threadIdx.x * AS_PX;
+    if (row >= H || colb >= W) return;
+    const float4 *vlab = lab + (size_t)z * N + (size_t)row * W;
+    uint32_t out[AS_PX];
+    int cluster_y = row / S;
+    int deltaY = (row + S / 2) / S - cluster_y;
+#pragma unroll
+    for (int p = 0; p < AS_PX; ++p) {
+        int col = colb + p;
+        out[p] = 0;
+        if (col >= W) continue;
+        float4 px = vlab[col];
+        int cluster_x = col / S;
+        int deltaX = (col + S / 2) / S - cluster_x;
+        float min_dist = 999999.9999f;
+        int min_id = -1;
+#pragma unroll
+        for (int i = -1; i <= 0; i++)
+#pragma unroll
+            for (int j = -1; j <= 0; j++) {
+                int cix = cluster_x + j + deltaY;   // column offset from the y phase
+                int ciy = cluster_y + i + deltaX;   // row offset from the x phase
+                if (cix >= 0 && ciy >= 0 && cix < mw && ciy < mh) {
+                    const float *c = s_ctr + 5 * ((ciy - ccy0) * ncx + (cix - ccx0));
+                    float dL = px.x - c[2], da = px.y - c[3], db = px.z - c[4];
+                    float color_distance = dL * dL + da * da + db * db;
+                    float dx = (float)col - c[0], dy = (float)row - c[1];
+                    float space_distance = dx * dx + dy * dy;
+                    float dist = sqrtf((color_distance * max_color_dist) + weight * (space_distance * max_xy_dist));
+                    if (dist < min_dist) { min_dist = dist; min_id = ciy * mw + cix; }
+                }
+            }
+        out[p] = (uint32_t)min_id;   // -1 -> 0xFFFFFFFF (only when no candidate cell exists)
+    }
+    uint32_t *o = idx + (size_t)z * N + (size_t)row * W + colb;
+    if (colb + AS_PX <= W && ((W & 3) == 0)) {
+        *reinterpret_cast<uint4 *>(o) = make_uint4(out[0], out[1], out[2], out[3]);
+    } else {
+#pragma unroll
+        for (int p = 0; p < AS_PX; ++p)
+            if (colb + p < W) o[p] = out[p];
+    }
+}
+
+int launch_assoc(const FrameDev &f, const SlicArgs &a, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    dim3 b(AS_TX / AS_PX, AS_TY);
+    dim3 g((f.W + AS_TX - 1) / AS_TX, (f.H + AS_TY - 1) / AS_TY, z1 - z0);
+    int ncx = (AS_TX - 1) / f.S + 4, ncy = (AS_TY - 1) / f.S + 4;
+    size_t sm = (size_t)ncx * ncy * 5 * sizeof(float);
+    if (f.S == 8)
+        k_assoc<8><<<g, b, sm, st>>>(f.lab, f.map, f.idx, f.W, f.H, f.mw, f.mh, f.S, f.N, f.M, z0, a.max_xy_dist,
+                                     a.max_color_dist, a.weight);
+    else if (f.S == 16)
+        k_assoc<16><<<g, b, sm, st>>>(f.lab, f.map, f.idx, f.W, f.H, f.mw, f.mh, f.S, f.N, f.M, z0, a.max_xy_dist,
+                                      a.max_color_dist, a.weight);
+    else
+        k_assoc<0><<<g, b, sm, st>>>(f.lab, f.map, f.idx, f.W, f.H, f.mw, f.mh, f.S, f.N, f.M, z0, a.max_xy_dist,
+                                     a.max_color_dist, a.weight);
+    return 1;
+}
+
+// ---------------------------------------------------------------------------------------
+// Centre update.  The reference runs one 16x16 work-group per (cluster, window tile g),
+// reduces 256 local-memory slots with the tree i = 128,64,...,1 and then adds the G
+// partials in g order (clcode.cl:584-596, 741-754).  The association of that float sum is
+// reproduced exactly by ONE WARP per cluster: lane l owns the eight slots l + 32k
+// (k = 0..7) of a window tile, folds them in registers in the order of tree steps 128, 64,
+// 32 and finishes steps 16..1 with shuffles.  Position and count sums are exact integers
+// (< 2^24), so they use integer warp reductions.  Window geometry, including the
+// under-coverage at S = 8 (cluster_per_line = 3S/16 = 1), follows clSLIC.cpp:22-23, 313
+// and clcode.cl:552-566.  finalize_reduction_result is fused: lane 0 divides and stores.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_update_centers(const float4 *__restrict__ lab,
+                                                        const uint32_t *__restrict__ idx, float4 *__restrict__ map,
+                                                        int W, int H, int mw, int mh, int S, int N, int M, int G,
+                                                        int cpl, int z0)
+{
+    int lane = threadIdx.x & 31;
+    int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    int z = z0 + blockIdx.y;
+    if (c >= M) return;
+    int gx = c % mw, gy = c / mw;
+    const uint32_t *vidx = idx + (size_t)z * N;
+    const float4 *vlab = lab + (size_t)z * N;
+    int lx = lane & 15, lyh = lane >> 4;
+    float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
+    int sx = 0, sy = 0, sn = 0;
+    for (int g = 0; g < G; ++g) {
+        int nbr_x = g % cpl, nbr_y = g / cpl;
+        int pxo = nbr_x * 16 + lx;
+        if (nbr_y * 16 >= S * 3) break;   // every slot of this and later tiles is empty: partial = +0
+        int px = gx * S - S + pxo;
+        bool colok = pxo < S * 3 && px >= 0 && px < W;
+        float v0[8], v1[8], v2[8];
+        int tx = 0, ty = 0, tn = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            int pyo = nbr_y * 16 + 2 * k + lyh;
+            int py = gy * S - S + pyo;
+            v0[k] = 0.0f; v1[k] = 0.0f; v2[k] = 0.0f;
+            if (colok && pyo < S * 3 && py >= 0 && py < H) {
+                size_t pi = (size_t)py * W + px;
+                if (vidx[pi] == (uint32_t)c) {
+                    float4 p = vlab[pi];
+                    v0[k] = p.x; v1[k] = p.y; v2[k] = p.z;
+                    tx += px; ty += py; tn += 1;
+                }
+            }
+        }
+        // tree steps 128, 64, 32 (slots differ by 4, 2, 1 in k)
+#pragma unroll
+        for (int h = 4; h >= 1; h >>= 1)
+#pragma unroll
+            for (int k = 0; k < h; ++k) { v0[k] += v0[k + h]; v1[k] += v1[k + h]; v2[k] += v2[k + h]; }
+        float a0 = v0[0], a1 = v1[0], a2 = v2[0];
+        // tree steps 16, 8, 4, 2, 1
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            a0 += __shfl_down_sync(0xffffffffu, a0, o);
+            a1 += __shfl_down_sync(0xffffffffu, a1, o);
+            a2 += __shfl_down_sync(0xffffffffu, a2, o);
+        }
+        sx += __reduce_add_sync(0xffffffffu, tx);
+        sy += __reduce_add_sync(0xffffffffu, ty);
+        sn += __reduce_add_sync(0xffffffffu, tn);
+        c0 = c0 + a0; c1 = c1 + a1; c2 = c2 + a2;   // only lane 0 holds the tree root
+    }
+    if (lane == 0) {
+        float4 *m = map + 2 * ((size_t)z * M + c);
+        float keep7 = m[1].w;   // s7 is not touched by SLIC
+        if (sn != 0) {
+            float n = (float)sn;
+            m[0] = make_float4((float)c, (float)sx / n, (float)sy / n, c0 / n);
+            m[1] = make_float4(c1 / n, c2 / n, n, keep7);
+        } else {
+            m[0] = make_float4((float)c, 0.0f, 0.0f, 0.0f);
+            m[1] = make_float4(0.0f, 0.0f, 0.0f, keep7);
+        }
+    }
+}
+
+int launch_update_centers(const FrameDev &f, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    int G = (int)ceilf((float)(f.S * f.S * 9) / 256.0f);
+    int cpl = f.S * 3 / 16;
+    dim3 g((f.M + 7) / 8, z1 - z0);
+    k_update_centers<<<g, 256, 0, st>>>(f.lab, f.idx, f.map, f.W, f.H, f.mw, f.mh, f.S, f.N, f.M, G, cpl, z0);
+    return 1;
+}
+
+// ---------------------------------------------------------------------------------------
+// Connectivity: 5x5 vote, last differing label wins, threshold >= 16, 2-pixel frame copied
+// (clcode.cl:676-711); two passes idx -> tmp -> idx (clSLIC.cpp:390-410).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_suppress(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, int W,
+                                                  int H, int N, int z0)
+{
+    int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+    int z = z0 + blockIdx.z;
+    if (x >= W || y >= H) return;
+    const uint32_t *vin = in + (size_t)z * N;
+    int id = W * y + x;
+    uint32_t cl = vin[id];
+    uint32_t res = cl;
+    if (!(x <= 1 || y <= 1 || x >= W - 2 || y >= H - 2)) {
+        int diff_count = 0;
+        uint32_t diff_lable = 0xFFFFFFFFu;
+#pragma unroll
+        for (int j = -2; j <= 2; j++)
+#pragma unroll
+            for (int i = -2; i <= 2; i++) {
+                uint32_t nl = vin[(y + j) * W + (x + i)];
+                if (nl != cl) { diff_lable = nl; diff_count++; }
+            }
+        if (diff_count >= 16) res = diff_lable;
+    }
+    out[(size_t)z * N + id] = res;
+}
+
+int launch_connectivity(const FrameDev &f, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    dim3 b(32, 8), g((f.W + 31) / 32, (f.H + 7) / 8, z1 - z0);
+    k_suppress<<<g, b, 0, st>>>(f.idx, f.idx_tmp, f.W, f.H, f.N, z0);
+    k_suppress<<<g, b, 0, st>>>(f.idx_tmp, f.idx, f.W, f.H, f.N, z0);
+    return 2;
+}
+
+} // namespace mvs

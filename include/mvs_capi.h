@@ -1,0 +1,148 @@
+/*
+ * mvs_capi.h -- C ABI of the B200-native per-view depth pipeline
+ * (SLIC -> block matching -> plane refinement -> fusion).
+ *
+ * The reference (kianoosh-j/CL_MultiView_Stereo, directory clMVDE/) has no C
+ * ABI: its stage classes call OpenCL directly.  This layer sits UNDER the kept
+ * C++ classes (include/clSLIC.h, photo_consistency.h, depth_refinement.h,
+ * pipeline.h) and is what a foreign-language binding (ctypes, cgo, JNI ...)
+ * binds.  Each entry point cites the reference interface it replaces.
+ *
+ * Conventions
+ *  - every function returns 0 on success, non-zero on failure;
+ *    mvs_last_error() returns a thread-local message for the last failure.
+ *  - there is NO CPU fallback: without a CUDA device every compute call fails.
+ *  - host pointers may be pageable; "dev" pointers are CUDA device pointers.
+ *  - layouts are the reference's:
+ *      rgbx   uchar4 {s0,s1,s2,pad}           [V][H][W]      (vec3u, file_handler.cpp:6-15)
+ *      lab    float4 {L,a,b,pad=0}            [V][H][W]      (vec3f)
+ *      idx    uint32 local superpixel index   [V][H][W]      (cl_uint)
+ *      map    float8 {id,cx,cy,L,a,b,n,disp}  [V][mh][mw]    (vec8f)
+ *      rep    uchar8 {nw,w,sw,n,s,ne,e,se}    [V][mh][mw]    (vec8u)
+ *      flat   float2                          [V][mh][mw]    (vec2f)
+ *      state  float[6] {d,sm,cs,nx,ny,nz}     [V][mh][mw]
+ *      disp   float                           [V][H][W]
+ */
+#ifndef MVS_CAPI_H
+#define MVS_CAPI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mvs_ctx mvs_ctx;       /* one CUDA device + streams (+ NCCL communicator) */
+typedef struct mvs_frame mvs_frame;   /* device-resident buffers of one V-view frame */
+
+/* Parameters of a frame.  Mirrors system_settings (header.h:55-77) plus the
+ * image geometry pipeline::pipeline derives (pipeline.cpp:15-19). */
+typedef struct mvs_params {
+    int width, height;           /* image size */
+    int spixl_size;              /* S */
+    int array_width, array_height;
+    float slic_color_weight;
+    int no_iter;
+    int enforce_connectivity;
+    int neib_hor, neib_ver;
+    int min_disp, max_disp, inc;
+    float bl_ratio;
+    int kernel_size;             /* as in system_settings (halved internally, pipeline.cpp:166) */
+    int kernel_step;
+    float fuse, gamma, alpha;    /* as in system_settings (2*g^2, 2*a^2 applied internally, pipeline.cpp:164-165) */
+    int no_prop;
+} mvs_params;
+
+/* selectors for mvs_frame_download / mvs_frame_upload / mvs_frame_dev_ptr */
+enum mvs_buffer {
+    MVS_BUF_RGBX = 0, MVS_BUF_LAB = 1, MVS_BUF_IDX = 2, MVS_BUF_MAP = 3, MVS_BUF_REP = 4,
+    MVS_BUF_FLAT = 5, MVS_BUF_STATE_A = 6, MVS_BUF_STATE_B = 7, MVS_BUF_DISP = 8
+};
+
+const char *mvs_last_error(void);
+int mvs_device_count(int *count);
+
+/* replaces pipeline::compile_device_code (pipeline.cpp:31-56): binds a device, creates streams */
+int mvs_ctx_create(int device, mvs_ctx **out);
+int mvs_ctx_destroy(mvs_ctx *ctx);
+int mvs_ctx_sync(mvs_ctx *ctx);
+/* number of kernel launches issued through this context so far */
+int mvs_ctx_launch_count(mvs_ctx *ctx, long long *count);
+/* the CUDA stream (cudaStream_t) every call on this context is ordered on */
+int mvs_ctx_stream(mvs_ctx *ctx, void **stream);
+/* page-locked host memory for the asynchronous copies */
+int mvs_host_alloc(void **p, size_t bytes);
+int mvs_host_free(void *p);
+
+/* multi-GPU: one process per GPU.  id is an opaque 128-byte NCCL unique id made by rank 0
+ * and distributed by the caller (torch.distributed / MPI / files). */
+int mvs_comm_unique_id(void *id128);
+int mvs_comm_init(mvs_ctx *ctx, const void *id128, int nranks, int rank);
+/* contiguous partition of V views over nranks (the plan mvs_frame_exchange assumes) */
+int mvs_view_partition(int V, int nranks, int rank, int *lo, int *hi);
+
+/* ---- frame: device-resident pipeline over V = array_width*array_height views ---- */
+/* view_lo..view_hi-1 are the views this context computes (all views for single GPU);
+ * buffers for every view are allocated because neighbour views are read (clcode.cl:1046,1314,1581). */
+int mvs_frame_create(mvs_ctx *ctx, const mvs_params *p, int view_lo, int view_hi, mvs_frame **out);
+int mvs_frame_destroy(mvs_frame *f);
+/* host <-> device copy of one buffer for views [v0,v1) */
+int mvs_frame_upload(mvs_frame *f, int which, int v0, int v1, const void *host);
+int mvs_frame_download(mvs_frame *f, int which, int v0, int v1, void *host);
+/* same, asynchronous on the context stream (host memory should be page-locked) */
+int mvs_frame_upload_async(mvs_frame *f, int which, int v0, int v1, const void *host);
+int mvs_frame_download_async(mvs_frame *f, int which, int v0, int v1, void *host);
+int mvs_frame_dev_ptr(mvs_frame *f, int which, void **dev);
+int mvs_frame_sizes(mvs_frame *f, int *V, int *W, int *H, int *mw, int *mh, int *num_levels);
+
+/* clSLIC::do_super_pixel_seg (clSLIC.cpp:67-122) for the frame's own views, all views per launch */
+int mvs_frame_slic(mvs_frame *f);
+/* clPhotoConsistency::do_initial_depth_estimation (photo_consistency.cpp:21-150):
+ * find_super_pixel_boundary + initial_depth_estimation_v2, writes rep and map.s7 */
+int mvs_frame_block_match(mvs_frame *f);
+/* clDepthRefinement::do_refinement (depth_refinement.cpp:91-118): flatness, init state,
+ * no_prop x propagate (ping-pong A/B), spixl_to_image from state A */
+int mvs_frame_refine(mvs_frame *f);
+/* the individual refinement stages (depth_refinement.cpp:122, 327, 724, 1318) */
+int mvs_frame_flatness(mvs_frame *f);
+int mvs_frame_init_state(mvs_frame *f);
+int mvs_frame_propagate(mvs_frame *f, int iter);
+int mvs_frame_fusion(mvs_frame *f);
+/* pipeline::exe_pipeline with perform_depth_est enabled (pipeline.cpp:60-64, 108-151) */
+int mvs_frame_run(mvs_frame *f);
+/* multi-GPU halo exchange of the buffers neighbouring views read (no-op without a communicator) */
+int mvs_frame_exchange(mvs_frame *f, int which);
+/* per-stage device time (ms) of the last mvs_frame_run: slic, boundary, block_match, flatness,
+ * init_state, propagate(total), fusion, exchange -- 8 floats */
+int mvs_frame_stage_ms(mvs_frame *f, float *ms8);
+/* stage timing events on/off (on by default for frames made by mvs_frame_create) */
+int mvs_frame_set_timing(mvs_frame *f, int enable);
+
+/* ---- class-level entry points with the reference's host-pointer semantics ---- */
+
+/* clSLIC::do_super_pixel_seg(in_img, cvt_img, spixl_map, idx_img) (clSLIC.h:19, clSLIC.cpp:67-122)
+ * for `count` images of the same size; outputs may be NULL to skip the copy back. */
+int mvs_slic_run(mvs_ctx *ctx, int width, int height, int spixl_size, float color_weight, int no_iter,
+                 int enforce_connectivity, int count, const void *rgbx, void *lab, void *map, uint32_t *idx);
+
+/* clPhotoConsistency::do_initial_depth_estimation (photo_consistency.h:10-19, .cpp:21-150).
+ * view_subset is the flattened int[V*V] (row stride V) and subset_num int[V] the reference
+ * builds at photo_consistency.cpp:39-47.  Fills rep and map[].s7. */
+int mvs_bm_run(mvs_ctx *ctx, int view_count, int width, int height, int spixl_size, float *map, uint8_t *rep,
+               const float *lab, const uint32_t *idx, int array_width, float bl_ratio, const int *view_subset,
+               const int *subset_num, const float *disp_levels, int num_levels);
+
+/* clDepthRefinement ctor + do_refinement (depth_refinement.h:6-9, .cpp:5-118).  gamma/alpha/
+ * kernel_size are the values pipeline::refine_depth_map passes (pipeline.cpp:164-166).
+ * Outputs (any may be NULL): flat float2[V*M], state_a/state_b float[6*V*M], disp float[V*N]. */
+int mvs_refine_run(mvs_ctx *ctx, int width, int height, int array_width, int array_height, int spixl_size,
+                   float bl_ratio, const float *map, const uint32_t *idx, const uint8_t *rep,
+                   const int *view_subset, const int *subset_num, float gamma, float alpha, float fuse,
+                   int kernel_step, int kernel_size, int no_prop, float *flat, float *state_a, float *state_b,
+                   float *disp);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

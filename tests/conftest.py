@@ -1,0 +1,26 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from tests import orc
+    return orc.load()
+
+
+@pytest.fixture(scope="session")
+def ctx():
+    import cl_multiview_stereo_b200 as mvs
+    c = mvs.Context(0)
+    yield c
+    c.close()
