@@ -113,6 +113,14 @@ class Context:
         check(lib().mvs_ctx_stream(self._h, C.byref(s)))
         return s.value or 0
 
+    def event_record(self, slot):
+        check(lib().mvs_ctx_event_record(self._h, int(slot)))
+
+    def event_elapsed_ms(self, a, b):
+        ms = C.c_float()
+        check(lib().mvs_ctx_event_elapsed(self._h, int(a), int(b), C.byref(ms)))
+        return ms.value
+
     @staticmethod
     def unique_id():
         buf = (C.c_char * 128)()

@@ -51,6 +51,7 @@ struct mvs_ctx {
     long long launches = 0;
     ncclComm_t comm = nullptr;
     int nranks = 1, rank = 0;
+    cudaEvent_t user_ev[16] = {nullptr};
 };
 
 enum { ST_SLIC = 0, ST_BOUNDARY, ST_BM, ST_FLAT, ST_INIT, ST_PROP, ST_FUSION, ST_EXCH, ST_COUNT };
@@ -101,6 +102,7 @@ extern "C" int mvs_ctx_destroy(mvs_ctx *c)
     if (!c) return 0;
     cudaSetDevice(c->device);
     if (c->comm) ncclCommDestroy(c->comm);
+    for (cudaEvent_t e : c->user_ev) if (e) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return 0;
@@ -125,6 +127,25 @@ extern "C" int mvs_ctx_stream(mvs_ctx *c, void **stream)
 {
     if (!c || !stream) return fail("null argument");
     *stream = (void *)c->stream;
+    return 0;
+}
+
+// CUDA-event timing on the context stream (what every launch of this context is ordered on)
+extern "C" int mvs_ctx_event_record(mvs_ctx *c, int slot)
+{
+    if (!c || slot < 0 || slot >= 16) return fail("bad event slot");
+    CK(cudaSetDevice(c->device));
+    if (!c->user_ev[slot]) CK(cudaEventCreate(&c->user_ev[slot]));
+    CK(cudaEventRecord(c->user_ev[slot], c->stream));
+    return 0;
+}
+
+extern "C" int mvs_ctx_event_elapsed(mvs_ctx *c, int a, int b, float *ms)
+{
+    if (!c || !ms || a < 0 || b < 0 || a >= 16 || b >= 16 || !c->user_ev[a] || !c->user_ev[b]) return fail("bad event slot");
+    CK(cudaSetDevice(c->device));
+    CK(cudaEventSynchronize(c->user_ev[b]));
+    CK(cudaEventElapsedTime(ms, c->user_ev[a], c->user_ev[b]));
     return 0;
 }
 

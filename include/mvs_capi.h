@@ -71,6 +71,9 @@ int mvs_ctx_sync(mvs_ctx *ctx);
 int mvs_ctx_launch_count(mvs_ctx *ctx, long long *count);
 /* the CUDA stream (cudaStream_t) every call on this context is ordered on */
 int mvs_ctx_stream(mvs_ctx *ctx, void **stream);
+/* CUDA-event timing on that stream: record into slot 0..15, elapsed ms between two slots */
+int mvs_ctx_event_record(mvs_ctx *ctx, int slot);
+int mvs_ctx_event_elapsed(mvs_ctx *ctx, int slot_a, int slot_b, float *ms);
 /* page-locked host memory for the asynchronous copies */
 int mvs_host_alloc(void **p, size_t bytes);
 int mvs_host_free(void *p);

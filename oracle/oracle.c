@@ -26,6 +26,19 @@
  */
 #include "oracle_math.h"
 #include <stdlib.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+/* host threads the oracle's OpenMP loops use (reported as cpu_baseline.cores) */
+int orc_num_threads(void)
+{
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
 
 #define LOCAL_SIZE_UPDATE 16 /* header.h:38 */
 
@@ -311,13 +324,13 @@ static inline int imax(int a, int b) { return a > b ? a : b; }
 /* kernel initial_depth_estimation_v2, clcode.cl:972-1069, for views z0..z1-1
  * (the reference launches it once per view, photo_consistency.cpp:133-140).
  * Writes only spixl_map[].s7. */
-void orc_block_match(const float *lab, float *map, const uint8_t *rep, const float *disp_level, int disp_num,
-                     const int *view_subset, const int *subset_num, int array_width, int V, int W, int H,
-                     int mw, int mh, float bl_ratio, int z0, int z1)
+void orc_block_match_rows(const float *lab, float *map, const uint8_t *rep, const float *disp_level, int disp_num,
+                          const int *view_subset, const int *subset_num, int array_width, int V, int W, int H,
+                          int mw, int mh, float bl_ratio, int z0, int z1, int y0, int y1)
 {
 #pragma omp parallel for schedule(dynamic, 64) collapse(2)
     for (int z = z0; z < z1; ++z)
-        for (int sp = 0; sp < mw * mh; ++sp) {
+        for (int sp = y0 * mw; sp < y1 * mw; ++sp) {
             size_t idx = (size_t)mw * mh * z + sp;
             const uint8_t *dir = rep + 8 * idx;
             int bb_l = imax(dir[0], imax(dir[1], dir[2]));
@@ -357,6 +370,14 @@ void orc_block_match(const float *lab, float *map, const uint8_t *rep, const flo
             }
             map[8 * idx + 7] = disp_est;
         }
+}
+
+void orc_block_match(const float *lab, float *map, const uint8_t *rep, const float *disp_level, int disp_num,
+                     const int *view_subset, const int *subset_num, int array_width, int V, int W, int H,
+                     int mw, int mh, float bl_ratio, int z0, int z1)
+{
+    orc_block_match_rows(lab, map, rep, disp_level, disp_num, view_subset, subset_num, array_width, V, W, H, mw, mh,
+                         bl_ratio, z0, z1, 0, mh);
 }
 
 /* pipeline::perform_depth_est, pipeline.cpp:121-142: disparity levels and the
@@ -730,16 +751,17 @@ static plane_t spatial_refinement(const rf_ctx *c, const float *state, const uin
 /* kernel propagate, clcode.cl:1727-1900, for views z0..z1-1 (all views' state_in
  * must be present: Jacobi update).  no_kernel_steps and kernel_step_size are
  * the per-iteration kernel arguments (depth_refinement.cpp:768-769). */
-void orc_propagate(float *state_out, const float *state_in, const float *map, const uint32_t *idx, const uint8_t *rep,
-                   const float *flat, const int *view_subset, const int *subset_num, int iter, int mw, int mh, int W,
-                   int H, float alpha, float gamma, float bl_ratio, float fuse, int no_kernel_steps,
-                   float kernel_step_size, int array_width, int V, int z0, int z1)
+void orc_propagate_rows(float *state_out, const float *state_in, const float *map, const uint32_t *idx,
+                        const uint8_t *rep, const float *flat, const int *view_subset, const int *subset_num, int iter,
+                        int mw, int mh, int W, int H, float alpha, float gamma, float bl_ratio, float fuse,
+                        int no_kernel_steps, float kernel_step_size, int array_width, int V, int z0, int z1, int y0,
+                        int y1)
 {
     rf_ctx c = {map, idx, rep, flat, view_subset, subset_num, V, W, H, mw, mh, array_width, gamma, alpha, bl_ratio, fuse};
     size_t M = (size_t)mw * mh;
-#pragma omp parallel for schedule(dynamic, 8) collapse(2)
+#pragma omp parallel for schedule(dynamic, 8) collapse(3)
     for (int z = z0; z < z1; ++z)
-        for (int y = 0; y < mh; ++y)
+        for (int y = y0; y < y1; ++y)
             for (int x = 0; x < mw; ++x) {
                 size_t id = M * z + (size_t)mw * y + x;
                 const float *sp = map + 8 * id;
@@ -787,6 +809,15 @@ void orc_propagate(float *state_out, const float *state_in, const float *map, co
                 float *so = state_out + 6 * id;
                 so[0] = p.d; so[1] = p.sm; so[2] = p.cs; so[3] = p.n.x; so[4] = p.n.y; so[5] = p.n.z;
             }
+}
+
+void orc_propagate(float *state_out, const float *state_in, const float *map, const uint32_t *idx, const uint8_t *rep,
+                   const float *flat, const int *view_subset, const int *subset_num, int iter, int mw, int mh, int W,
+                   int H, float alpha, float gamma, float bl_ratio, float fuse, int no_kernel_steps,
+                   float kernel_step_size, int array_width, int V, int z0, int z1)
+{
+    orc_propagate_rows(state_out, state_in, map, idx, rep, flat, view_subset, subset_num, iter, mw, mh, W, H, alpha,
+                       gamma, bl_ratio, fuse, no_kernel_steps, kernel_step_size, array_width, V, z0, z1, 0, mh);
 }
 
 /* kernel spixl_to_image, clcode.cl:1906-1931 */

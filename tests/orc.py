@@ -156,6 +156,27 @@ class Oracle:
                                z0, z1)
         return out
 
+    def num_threads(self):
+        return int(self.lib.orc_num_threads())
+
+    def block_match_rows(self, lab, mp, rep, levels, subset, subset_num, aw, bl_ratio, z, y0, y1):
+        """timing helper: rows [y0,y1) of view z, result written into a copy"""
+        V, H, W, _ = lab.shape
+        mh, mw = mp.shape[1:3]
+        mp = mp.copy()
+        self.lib.orc_block_match_rows(_p(lab), _p(mp), _p(rep), _p(levels), len(levels), _p(subset), _p(subset_num), aw,
+                                      V, W, H, mw, mh, _cf(bl_ratio), z, z + 1, y0, y1)
+        return mp
+
+    def propagate_rows(self, st_in, out, mp, idx, rep, flat, subset, subset_num, it, aw, bl_ratio, gamma, alpha, fuse,
+                       ksteps, kss, z, y0, y1):
+        V, H, W = idx.shape
+        mh, mw = mp.shape[1:3]
+        self.lib.orc_propagate_rows(_p(out), _p(st_in), _p(mp), _p(idx), _p(rep), _p(flat), _p(subset), _p(subset_num),
+                                    it, mw, mh, W, H, _cf(alpha), _cf(gamma), _cf(bl_ratio), _cf(fuse), ksteps, _cf(kss),
+                                    aw, V, z, z + 1, y0, y1)
+        return out
+
     def spixl_to_image(self, mp, idx, st):
         V, H, W = idx.shape
         mh, mw = mp.shape[1:3]
