@@ -863,3 +863,13 @@ void orc_refine(const float *map, const uint32_t *idx, const uint8_t *rep, const
     }
     orc_spixl_to_image(map, idx, state_a, disp, V, W, H, mw, mh);
 }
+
+/* ------------------------------------------------------------------------ */
+/* vector wrappers of the pinned math (tests compare them with libm and with
+ * the CUDA copy in csrc/mvs_math.cuh)                                       */
+/* ------------------------------------------------------------------------ */
+void orc_math_expf(const float *x, float *y, int n) { for (int i = 0; i < n; ++i) y[i] = o_expf(x[i]); }
+void orc_math_exp(const double *x, double *y, int n) { for (int i = 0; i < n; ++i) y[i] = o_exp(x[i]); }
+void orc_math_cbrtf(const float *x, float *y, int n) { for (int i = 0; i < n; ++i) y[i] = o_cbrtf_pos(x[i]); }
+void orc_math_roundf(const float *x, float *y, int n) { for (int i = 0; i < n; ++i) y[i] = o_roundf(x[i]); }
+void orc_math_f2i(const float *x, int *y, int n) { for (int i = 0; i < n; ++i) y[i] = o_f2i(x[i]); }
