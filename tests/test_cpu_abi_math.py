@@ -1,0 +1,122 @@
+"""CPU tests (no GPU): the C-ABI library loads and exports every symbol include/mvs_capi.h
+declares (no compute calls), the host-side helpers agree with the oracle's restatement of
+pipeline.cpp:121-142, and the oracle's pinned math sits within a few ULP of libm."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import cl_multiview_stereo_b200 as mvs
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    txt = open(os.path.join(ROOT, "include", "mvs_capi.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(mvs_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_header_declares_what_python_binds():
+    assert set(header_symbols()) == set(mvs.SYMBOLS)
+
+
+def test_library_exports_every_declared_symbol():
+    lib = mvs.lib()
+    for s in header_symbols():
+        assert hasattr(lib, s), f"libmvs_b200.so does not export {s}"
+
+
+def test_params_struct_layout():
+    # mvs_params: 20 four-byte fields, no padding
+    assert C.sizeof(mvs.Params) == 80
+
+
+def test_no_cpu_fallback_without_device():
+    """without a CUDA device every compute entry point fails loudly"""
+    lib = mvs.lib()
+    n = C.c_int(-1)
+    rc = lib.mvs_device_count(C.byref(n))
+    if rc == 0 and n.value > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(mvs.MvsError):
+        mvs.Context(0)
+
+
+def test_view_partition_covers_all_views():
+    for V in (1, 9, 15, 16, 25):
+        for n in (1, 2, 4, 8):
+            spans = [mvs.view_partition(V, n, r) for r in range(n)]
+            assert spans[0][0] == 0 and spans[-1][1] == V
+            for a, b in zip(spans, spans[1:]):
+                assert a[1] == b[0]
+            sizes = [hi - lo for lo, hi in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_levels_and_subsets_match_oracle(oracle):
+    # pipeline.cpp:121-124 and :130-142 (x outer, y inner, self excluded)
+    assert np.array_equal(mvs.make_levels(30, 60, 1), oracle.make_levels(30, 60, 1))
+    assert len(mvs.make_levels(10, 100, 2)) == 46
+    for aw, ah in ((5, 3), (3, 3), (4, 4), (1, 1), (5, 5)):
+        sub, num = mvs.make_subsets(aw, ah)
+        osub, onum = oracle.make_subsets(aw, ah)
+        assert np.array_equal(num, onum)
+        for z in range(aw * ah):
+            assert np.array_equal(sub[z, :num[z]], osub[z, :onum[z]])
+    sub, num = mvs.make_subsets(5, 3)
+    assert list(sub[6, :num[6]]) == [0, 5, 10, 1, 11, 2, 7, 12]
+
+
+def ulp_diff(a, b):
+    a = np.asarray(a, np.float32).view(np.int32).astype(np.int64)
+    b = np.asarray(b, np.float32).view(np.int32).astype(np.int64)
+    a = np.where(a < 0, -(a & 0x7FFFFFFF), a)
+    b = np.where(b < 0, -(b & 0x7FFFFFFF), b)
+    return np.abs(a - b)
+
+
+def test_pinned_expf_close_to_libm(oracle):
+    rng = np.random.default_rng(1)
+    x = np.concatenate([rng.uniform(-87, 88, 200000), rng.uniform(-2, 2, 100000), [0.0, -0.0, 1.0, -1.0]]).astype(np.float32)
+    y = np.empty_like(x)
+    oracle.lib.orc_math_expf(x.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p), len(x))
+    want = np.exp(x.astype(np.float64)).astype(np.float32)
+    assert ulp_diff(y, want).max() <= 2
+    # edges: overflow, underflow, NaN
+    e = np.array([89.0, 1000.0, -104.5, -1000.0, np.nan, -100.0], np.float32)
+    r = np.empty_like(e)
+    oracle.lib.orc_math_expf(e.ctypes.data_as(C.c_void_p), r.ctypes.data_as(C.c_void_p), len(e))
+    assert np.isinf(r[0]) and np.isinf(r[1]) and r[2] == 0 and r[3] == 0 and np.isnan(r[4])
+    assert r[5] > 0 and ulp_diff(r[5:6], np.float32(np.exp(-100.0))).max() <= 1   # denormal result
+
+
+def test_pinned_exp_double_close_to_libm(oracle):
+    rng = np.random.default_rng(2)
+    x = rng.uniform(-50, 50, 100000)
+    y = np.empty_like(x)
+    oracle.lib.orc_math_exp(x.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p), len(x))
+    assert np.max(np.abs(y / np.exp(x) - 1)) < 5e-16
+
+
+def test_pinned_cbrt_close_to_libm(oracle):
+    rng = np.random.default_rng(3)
+    x = np.concatenate([rng.uniform(0.008856, 1.2, 200000), [0.008857, 1.0, 0.125, 8.0]]).astype(np.float32)
+    y = np.empty_like(x)
+    oracle.lib.orc_math_cbrtf(x.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p), len(x))
+    want = np.cbrt(x.astype(np.float64)).astype(np.float32)
+    assert ulp_diff(y, want).max() <= 1
+    assert y[-3] == 1.0 and y[-2] == 0.5 and y[-1] == 2.0
+
+
+def test_round_and_truncation_semantics(oracle):
+    x = np.array([0.5, -0.5, 1.5, 2.5, -2.5, 0.49999997, -0.9, 0.9, 3e9, -3e9, np.nan], np.float32)
+    r = np.empty_like(x)
+    oracle.lib.orc_math_roundf(x.ctypes.data_as(C.c_void_p), r.ctypes.data_as(C.c_void_p), len(x))
+    assert list(r[:8]) == [1.0, -1.0, 2.0, 3.0, -3.0, 0.0, -1.0, 1.0]      # half away from zero (R4)
+    i = np.empty(len(x), np.int32)
+    oracle.lib.orc_math_f2i(x.ctypes.data_as(C.c_void_p), i.ctypes.data_as(C.c_void_p), len(x))
+    assert list(i[:8]) == [0, 0, 1, 2, -2, 0, 0, 0]                          # toward zero (B5)
+    assert i[8] == 2147483647 and i[9] == -2147483648 and i[10] == 0          # cvt.rzi saturation
