@@ -609,7 +609,9 @@ extern "C" int mvs_frame_propagate(mvs_frame *f, int iter)
     StageTimer t(f, ST_PROP);
     // per-iteration arguments, depth_refinement.cpp:768-769 (int / int, float / int)
     RefineArgs a{f->gamma, f->alpha, f->fuse, f->bl_ratio, f->kernel_step / (iter + 1), f->kss / (float)(iter + 1), iter};
-    f->ctx->launches += launch_propagate(f->d, a, src, dst, f->lo, f->hi, f->ctx->stream);
+    int nl = launch_propagate(f->d, a, src, dst, f->lo, f->hi, f->ctx->stream);
+    if (nl < 0) return fail("propagate: kernel_step %d needs more shared memory than one SM has", a.no_kernel_steps);
+    f->ctx->launches += nl;
     return check_launch("propagate");
 }
 
