@@ -32,11 +32,17 @@ constexpr int PR_SPB = PR_WARPS * PR_OCT;   // superpixels per CTA
 constexpr int PR_ITEMS = 72;                // 9 samples x 8 neighbour views at most
 
 // shared-memory record of one superpixel (dynamic: tab/prod hold tmax entries)
+constexpr int PR_MEMO = 4;                  // evaluated planes remembered per superpixel
+
 struct SpShared {
-    float4 samp[9];          // {sx (int bits), sy (int bits), cx - sx, cy - sy}
-    float4 viewt[8];         // {view (int bits), dvx, dvy, 0}
+    float4 samp[9];          // {sx, sy (integers held as float), cx - sx, cy - sy}
+    float4 viewt[8];         // {view * N (int bits), dvx, dvy, view * M (int bits)}
     float2 item[PR_ITEMS];   // per (view, sample): {visible term or flag, visibility term or -1}
+    float2 di[10];           // per sample of the current candidate: {d_intrp, bl_ratio * d_intrp}
+    float4 memo_plane[PR_MEMO];   // {d, nx, ny, nz} of the last evaluated candidates
+    float2 memo_cost[PR_MEMO];    // their {smoothness, consistency}
 };
+static_assert(sizeof(SpShared) % 16 == 0, "SpShared must keep float4 alignment");
 
 __host__ __device__ inline size_t sp_shared_bytes(int tmax)
 {
@@ -76,6 +82,18 @@ __device__ __forceinline__ void near_offset(int s, int &i, int &j)
     j = t % 3 - 1;
 }
 
+// acceptance test shared by update() and spatialRefinement() (clcode.cl:1663-1669,
+// 1713-1718): update() weighs sm1 by the colour similarity to the source neighbour,
+// spatialRefinement() does not (wsim = 1, exact) and keeps d (its cd IS the current d)
+__device__ __forceinline__ void accept(int iter, bool, float sm1, float cs1, float wsim, float cd, float cnx,
+                                       float cny, float cnz, float &pd, float &pnx, float &pny, float &pnz,
+                                       float &psm, float &pcs)
+{
+    if ((iter < 4 && sm1 * wsim > psm) || cs1 * sm1 > psm * pcs) {
+        pd = cd; psm = sm1; pcs = cs1; pnx = cnx; pny = cny; pnz = cnz;
+    }
+}
+
 } // namespace
 
 __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
@@ -103,6 +121,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
     const float2 fl = a.flat[zM + sp];
     const int ns = a.subset_num[z];
     const int camx = z % a.aw, camy = z / a.aw;
+    const double half_fly = 0.5 * (double)fl.y;   // clcode.cl:1621 is a double expression
 
     // sample table: sample k = (i+1)*3 + (j+1) sits s_k pixels along ray (i, j) from the
     // truncated centre (clcode.cl:1547-1566); rep bytes are {nw,w,sw,n,s,ne,e,se}
@@ -113,11 +132,13 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
         for (int k = l8; k < 9; k += 8) {
             int s = k == 4 ? 0 : (int)((r64 >> (8 * (k < 4 ? k : k - 1))) & 255);
             int sx = icx + s * (k / 3 - 1), sy = icy + s * (k % 3 - 1);
-            sh->samp[k] = make_float4(__int_as_float(sx), __int_as_float(sy), cx - (float)sx, cy - (float)sy);
+            // |sx|, |sy| < 2^24: the float copies are exact
+            sh->samp[k] = make_float4((float)sx, (float)sy, cx - (float)sx, cy - (float)sy);
         }
         if (l8 < ns) {
             int view = a.view_subset[a.V * z + l8];
-            sh->viewt[l8] = make_float4(__int_as_float(view), (float)(view % a.aw - camx), (float)(view / a.aw - camy), 0.0f);
+            sh->viewt[l8] = make_float4(__int_as_float(view * a.N), (float)(view % a.aw - camx),
+                                        (float)(view / a.aw - camy), __int_as_float(view * a.M));
         }
     }
 
@@ -178,24 +199,32 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
     const int far_end = 8 + 4 * a.K, ncand = far_end + 8;
     const bool far_possible = stride < max(a.mw, a.mh);
     int ci = live ? 0 : ncand;
+    int nmemo = 0;   // planes evaluated so far by this octet (memo holds the last PR_MEMO)
 
     for (;;) {
-        // next in-range candidate of this octet
+        // ---- next candidate of this octet that still needs an evaluation ----
+        // A candidate's costs are a pure function of its plane (cd, cn) for the fixed input
+        // state, and neighbouring superpixels often carry bit-identical planes: planes already
+        // evaluated for this superpixel take their costs from the memo and go straight to the
+        // acceptance test.
         bool act = false, pair = false;
-        int q1 = 0, q2 = 0;
+        float cd = 0.0f, cnx = 0.0f, cny = 0.0f, cnz = 0.0f, wsim = 1.0f;
         while (ci < ncand && !act) {
             const int c = ci++;
+            int q1 = 0, q2 = 0;
+            bool ok;
+            pair = false;
             if (c < 8) {
                 int i, j;
                 near_offset(c, i, j);
-                act = cell(a, x + i, y + j, q1);
+                ok = cell(a, x + i, y + j, q1);
             } else if (c < far_end) {
                 if (!far_possible) { ci = far_end; continue; }
                 const int off = (1 + ((c - 8) >> 2)) * stride, dir = (c - 8) & 3;
-                if (dir == 0) { act = y > off; q1 = a.mw * (y - (off + 1)) + x; }
-                else if (dir == 1) { act = y < a.mh - off - 1; q1 = a.mw * (y + off + 1) + x; }
-                else if (dir == 2) { act = x > off; q1 = a.mw * y + x - off - 1; }
-                else { act = x < a.mw - off - 1; q1 = a.mw * y + x + off + 1; }
+                if (dir == 0) { ok = y > off; q1 = a.mw * (y - (off + 1)) + x; }
+                else if (dir == 1) { ok = y < a.mh - off - 1; q1 = a.mw * (y + off + 1) + x; }
+                else if (dir == 2) { ok = x > off; q1 = a.mw * y + x - off - 1; }
+                else { ok = x < a.mw - off - 1; q1 = a.mw * y + x + off + 1; }
             } else {
                 const int r = c - far_end, r2 = (r + 1) & 7;
                 // ring position r -> offset: W,NW,N,NE,E,SE,S,SW
@@ -204,16 +233,11 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
                 const int ox2 = (r2 == 0 || r2 == 1 || r2 == 7) ? -1 : ((r2 >= 3 && r2 <= 5) ? 1 : 0);
                 const int oy2 = (r2 >= 1 && r2 <= 3) ? -1 : ((r2 >= 5) ? 1 : 0);
                 const bool ok1 = cell(a, x + ox1, y + oy1, q1), ok2 = cell(a, x + ox2, y + oy2, q2);
-                act = ok1 && ok2;
+                ok = ok1 && ok2;
                 pair = true;
             }
-        }
-        if (!__any_sync(FULL, act)) break;
-        __syncwarp();   // the previous candidate's staged terms have been consumed
-
-        // ---- the candidate plane (cd, cn) and its acceptance weight ----
-        float cd = 0.0f, cnx = 0.0f, cny = 0.0f, cnz = 0.0f, wsim = 1.0f;
-        if (act) {
+            if (!ok) continue;
+            // the candidate plane (cd, cn) and its acceptance weight
             if (!pair) {   // update(): neighbour's plane extrapolated to the own centre (clcode.cl:1643-1651)
                 const float4 pl = vp[q1];
                 const float4 qa = vm[2 * q1], qb = vm[2 * q1 + 1];
@@ -229,29 +253,51 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
                 const float cry = bx * az - ax * bz;
                 const float crz = ax * by - ay * bx;
                 const float len = sqrtf(crx * crx + cry * cry + crz * crz + 0.0f * 0.0f);
+                cnx = 0.0f; cny = 0.0f; cnz = 0.0f;
                 if (len != 0.0f) { cnx = crx / len; cny = cry / len; cnz = crz / len; }
                 cd = pd;
+                wsim = 1.0f;
             }
+            bool hit = false;
+            for (int e = 0; e < min(nmemo, PR_MEMO) && !hit; ++e) {
+                const float4 mp = sh->memo_plane[e];
+                if (__float_as_int(mp.x) == __float_as_int(cd) && __float_as_int(mp.y) == __float_as_int(cnx) &&
+                    __float_as_int(mp.z) == __float_as_int(cny) && __float_as_int(mp.w) == __float_as_int(cnz)) {
+                    const float2 mc = sh->memo_cost[e];
+                    accept(a.iter, pair, mc.x, mc.y, wsim, cd, cnx, cny, cnz, pd, pnx, pny, pnz, psm, pcs);
+                    hit = true;
+                }
+            }
+            act = !hit;
         }
+        if (!__any_sync(FULL, act)) break;
 
-        // ---- compute_consistency items: (neighbour view n, sample k) spread over the octet ----
+        // ---- per-sample plane disparity of the candidate (clcode.cl:1571-1573), once per sample ----
+        if (act)
+            for (int k = l8; k < 9; k += 8) {
+                const float4 sv = sh->samp[k];
+                const float di = (cnx * sv.z + cny * sv.w + cnz * cd) / cnz;
+                sh->di[k] = make_float2(di, a.bl_ratio * di);
+            }
+        __syncwarp();
+
         if (act) {
+            // ---- compute_consistency items: (neighbour view n, sample k) spread over the octet ----
             const int nitems = 9 * ns;
             for (int it = l8; it < nitems; it += 8) {
                 const int n = it / 9, k = it - 9 * n;
                 const float4 sv = sh->samp[k], vt = sh->viewt[n];
-                const int sx = __float_as_int(sv.x), sy = __float_as_int(sv.y), view = __float_as_int(vt.x);
-                const float di = (cnx * sv.z + cny * sv.w + cnz * cd) / cnz;      // clcode.cl:1571-1573
-                const int xp = f2i((float)sx - round_haz(di * vt.y));            // :1576
-                const int yp = f2i((float)sy - round_haz((a.bl_ratio * di) * vt.z));
-                float2 out = make_float2(0.0f, -1.0f);                            // -1: sample projects outside
+                const float2 dd = sh->di[k];
+                const int xp = f2i(sv.x - round_haz(dd.x * vt.y));   // clcode.cl:1576-1577
+                const int yp = f2i(sv.y - round_haz(dd.y * vt.z));
+                float2 out = make_float2(0.0f, -1.0f);              // -1: sample projects outside
                 if (xp >= 0 && yp >= 0 && xp < a.W && yp < a.H) {
-                    const uint32_t q = a.idx[(size_t)view * a.N + (size_t)yp * a.W + xp];
-                    const float4 *pm = a.map + 2 * ((size_t)view * a.M + q);
-                    const float4 qa = pm[0], qb = pm[1];
-                    const float4 pl = a.plane_in[(size_t)view * a.M + q];
+                    const uint32_t q = a.idx[(uint32_t)__float_as_int(vt.x) + (uint32_t)(yp * a.W + xp)];
+                    const uint32_t vq = (uint32_t)__float_as_int(vt.w) + q;
+                    const float4 qa = a.map[2 * vq], qb = a.map[2 * vq + 1];
+                    const float4 pl = a.plane_in[vq];
                     const float d_proj = (pl.y * (qa.y - (float)xp) + pl.z * (qa.z - (float)yp) + pl.w * pl.x) / pl.w;
-                    const float diff = d_proj - di;
+                    const float diff = d_proj - dd.x;
                     // visible: exp term; occluded: -1 (adds +0 in the reference); NaN stays NaN
                     out.x = fabsf(diff) < a.fuse ? expf_pinned(-diff * diff * a.alpha) : (diff != diff ? diff : -1.0f);
                     const float cdiff = dist3(qa.w, qb.x, qb.y, cL, ca, cb);
@@ -299,21 +345,28 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
             if (fn & 1) {
                 view_counter++;
                 if (fn & 2) consistency += tn;
-                if (fn & 4) consistency = (float)((double)consistency + 0.5 * (double)fl.y);
+                if (fn & 4) consistency = (float)((double)consistency + half_fly);
             }
         }
         if (act) {
             const float margin = (float)0.01;
             const float cs1 = view_counter > 0 ? fmaxf(margin, consistency / (float)view_counter) : margin;
             float smoothness = 0.0f;
-            for (int t = 0; t < T; ++t) smoothness += prod[t];
-            const float sm1 = weight_norm > 0.0f ? smoothness / weight_norm : (float)0.000001;
-            // acceptance: update() weighs sm1 by the colour similarity, spatialRefinement() does not
-            // and keeps d (clcode.cl:1663-1669, 1713-1718)
-            if ((a.iter < 4 && sm1 * wsim > psm) || cs1 * sm1 > psm * pcs) {
-                pd = cd; psm = sm1; pcs = cs1; pnx = cnx; pny = cny; pnz = cnz;
+            int t = 0;
+            for (; t + 4 <= T; t += 4) {
+                const float4 p4 = *reinterpret_cast<const float4 *>(prod + t);
+                smoothness += p4.x; smoothness += p4.y; smoothness += p4.z; smoothness += p4.w;
             }
+            for (; t < T; ++t) smoothness += prod[t];
+            const float sm1 = weight_norm > 0.0f ? smoothness / weight_norm : (float)0.000001;
+            if (l8 == 0) {
+                sh->memo_plane[nmemo % PR_MEMO] = make_float4(cd, cnx, cny, cnz);
+                sh->memo_cost[nmemo % PR_MEMO] = make_float2(sm1, cs1);
+            }
+            nmemo++;
+            accept(a.iter, pair, sm1, cs1, wsim, cd, cnx, cny, cnz, pd, pnx, pny, pnz, psm, pcs);
         }
+        __syncwarp();   // staged terms consumed, memo visible to the octet
     }
 
     if (live && l8 == 0) {
@@ -321,6 +374,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
         a.cost_out[zM + sp] = make_float2(psm, pcs);
     }
 }
+
 
 int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, int z0, int z1, cudaStream_t st)
 {
@@ -335,7 +389,7 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     a.kernel_step_size = r.kernel_step_size; a.iter = r.iter; a.z0 = z0;
     a.tmax = 8 + 4 * a.K;
     size_t smem = PR_SPB * sp_shared_bytes(a.tmax);
-    if (smem > 227 * 1024) return -1;   // kernel_step too large for the staged term table
+    if (smem > 227 * 1024 || (double)f.V * f.N >= 2147483648.0) return -1;   // kernel_step too large for the staged term table
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 g((f.mw + PR_OCT - 1) / PR_OCT, (f.mh + PR_WARPS - 1) / PR_WARPS, z1 - z0);
     k_propagate<<<g, PR_WARPS * 32, smem, st>>>(a);
