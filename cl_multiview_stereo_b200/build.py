@@ -51,6 +51,15 @@ def build_native(force=False, verbose=False):
             if verbose:
                 print(" ".join(cmd))
             subprocess.check_call(cmd)
+    # the reference-shaped entry point (examples/clMVDE.cpp ~ reference clMVDE.cpp:12-43)
+    ex_src = os.path.join(ROOT, "examples", "clMVDE.cpp")
+    ex_bin = os.path.join(ROOT, "examples", "clMVDE")
+    if os.path.exists(ex_src) and os.path.exists(HOSTLIB) and (force or _newer(ex_bin, [ex_src, HOSTLIB, LIB])):
+        cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "include"), "-o", ex_bin, ex_src,
+               "-L", PKG, "-lmvs_host", "-lmvs_b200", "-Wl,-rpath,$ORIGIN/../cl_multiview_stereo_b200"]
+        if verbose:
+            print(" ".join(cmd))
+        subprocess.check_call(cmd)
     return LIB
 
 

@@ -1,0 +1,118 @@
+"""Pins the CPU oracle (oracle/oracle.c) to the reference itself.
+
+  * live: the reference's own device source, clcode.cl compiled as C++ (oracle/ref ->
+    oracle/_ref/libclref.so), is run beside the restatement on seeded inputs -- every stage must
+    agree bit for bit.  Needs /root/reference at build time; skipped where it never existed.
+  * golden: tests/golden/*.npz hold outputs that libclref produced here
+    (tests/golden/make_golden.py); the restatement must reproduce them bit for bit anywhere.
+"""
+import glob
+import json
+import os
+
+import numpy as np
+import pytest
+
+import cl_multiview_stereo_b200 as mvs
+from cl_multiview_stereo_b200 import synth
+from tests import clref
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def assert_same(got, want, what):
+    got, want = np.asarray(got), np.asarray(want)
+    assert got.shape == want.shape, f"{what}: shape {got.shape} vs {want.shape}"
+    if got.dtype == np.float32:
+        neq = (bits(got) != bits(want)) & ~(np.isnan(got) & np.isnan(want))
+    else:
+        neq = got != want
+    if neq.any():
+        k = tuple(np.argwhere(neq)[0])
+        raise AssertionError(f"{what}: {int(neq.sum())} of {neq.size} differ, first at {k}: {got[k]!r} vs {want[k]!r}")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    r = clref.load()
+    if r is None:
+        pytest.skip("oracle/_ref/libclref.so absent and /root/reference not present to build it")
+    return r
+
+
+@pytest.mark.parametrize("W,H,S,conn,iters", [(64, 48, 8, False, 2), (45, 37, 8, True, 1), (64, 48, 16, False, 1),
+                                              (50, 40, 10, False, 1)])
+def test_slic_restatement_equals_reference_source(oracle, ref, W, H, S, conn, iters):
+    img = synth.voronoi_image(W + S, W, H, sites=18)
+    mxy, mcol = oracle.slic_params(S)
+    lab_r, mp_r, idx_r = ref.slic(img, S, 0.6, iters, conn, mxy, mcol)
+    lab_o, mp_o, idx_o = oracle.slic(img, S, 0.6, iters, conn)
+    assert_same(lab_o, lab_r, "lab")
+    assert_same(idx_o, idx_r, "labels")
+    assert_same(mp_o, mp_r, "spixl_map")
+
+
+@pytest.mark.parametrize("aw,ah,W,H,bl,levels,ksize", [(3, 2, 96, 64, 1.0, (0, 16, 1), 128), (2, 2, 77, 53, 0.625, (2, 40, 2), 64),
+                                                       (5, 3, 64, 48, 1.0359, (0, 12, 1), 1080)])
+def test_depth_restatement_equals_reference_source(oracle, ref, aw, ah, W, H, bl, levels, ksize):
+    """block matching, flatness, init state, every propagate iteration, fusion"""
+    s = mvs.SystemSettings(array_width=aw, array_height=ah, min_disp=levels[0], max_disp=levels[1], inc=levels[2],
+                           bl_ratio=bl, kernel_size=ksize)
+    rgbx, _ = synth.make_frame(aw * 10 + ah, W, H, aw, ah, bl_ratio=bl, n_patches=4, dmin=levels[0] + 2,
+                               dmax=min(levels[1] - 2, 14))
+    o = oracle.pipeline(rgbx, s)          # SLIC by the restatement (checked against the source above)
+    S = s.spixl_size
+    lv = oracle.make_levels(s.min_disp, s.max_disp, s.inc)
+    sub, num = oracle.make_subsets(aw, ah)
+    assert_same(o["rep"], ref.boundary(o["map_slic"], o["idx"], S), "spixl_rep")
+    assert_same(o["map"], ref.block_match(o["lab"], o["map_slic"], o["rep"], o["idx"], lv, sub, num, aw, bl, S), "initD")
+    g_, a_ = np.float32(2 * s.gamma ** 2), np.float32(2 * s.alpha ** 2)
+    gam, alp, fus, kss = oracle.refine_params(g_, a_, s.fuse, s.kernel_step, s.kernel_size // 2, S)
+    assert_same(o["flat"], ref.flatness(o["map"], np.float32(1.0 / float(g_))), "flatness")
+    st_o = oracle.init_state(o["map"], o["idx"], o["rep"], o["flat"], sub, num, aw, bl, gam, alp, fus, s.kernel_step, kss)
+    st_r = ref.init_state(o["map"], o["idx"], o["rep"], o["flat"], sub, num, aw, bl, gam, alp, fus, s.kernel_step, kss)
+    assert_same(st_o, st_r, "init state")
+    for it in range(s.no_prop):
+        args = (o["map"], o["idx"], o["rep"], o["flat"], sub, num, it, aw, bl, gam, alp, fus, s.kernel_step // (it + 1),
+                np.float32(kss) / np.float32(it + 1))
+        nxt_o, nxt_r = oracle.propagate(st_o, *args), ref.propagate(st_o, *args)
+        assert_same(nxt_o, nxt_r, f"state after propagate {it}")
+        st_o = nxt_o
+    assert_same(o["disp"], ref.spixl_to_image(o["map"], o["idx"], o["state_a"]), "disparity")
+
+
+def golden_files(prefix):
+    return sorted(glob.glob(os.path.join(GOLDEN, prefix + "*.npz")))
+
+
+def settings_from(g):
+    d = json.loads(str(g["settings"]))
+    return mvs.SystemSettings(**d)
+
+
+@pytest.mark.parametrize("path", golden_files("synth_") + golden_files("bar_"), ids=os.path.basename)
+def test_restatement_reproduces_pipeline_golden(oracle, path):
+    g = np.load(path)
+    s = settings_from(g)
+    o = oracle.pipeline(g["rgbx"], s)
+    for k in ("idx", "map_slic", "rep", "map", "flat", "state_a", "state_b", "disp"):
+        assert_same(o[k], g[k], f"{os.path.basename(path)}:{k}")
+
+
+@pytest.mark.parametrize("path", golden_files("slic_"), ids=os.path.basename)
+def test_restatement_reproduces_slic_golden(oracle, path):
+    g = np.load(path)
+    lab, mp, idx = oracle.slic(g["rgbx"], int(g["S"]), float(g["weight"]), int(g["no_iter"]), bool(g["connectivity"]))
+    assert_same(lab, g["lab"], "lab")
+    assert_same(idx, g["idx"], "labels")
+    assert_same(mp, g["map"], "spixl_map")
+
+
+def test_golden_set_is_present():
+    names = {os.path.basename(p) for p in glob.glob(os.path.join(GOLDEN, "*.npz"))}
+    assert {"synth_3x2.npz", "bar_5x3_crop.npz", "slic_dance_s8_conn.npz", "slic_horse_s16.npz",
+            "slic_horse_s8.npz"} <= names
