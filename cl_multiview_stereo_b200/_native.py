@@ -28,7 +28,7 @@ class Params(C.Structure):
 SYMBOLS = [
     "mvs_last_error", "mvs_device_count", "mvs_ctx_create", "mvs_ctx_destroy", "mvs_ctx_sync",
     "mvs_ctx_launch_count", "mvs_ctx_stream", "mvs_ctx_event_record", "mvs_ctx_event_elapsed", "mvs_comm_unique_id", "mvs_comm_init", "mvs_host_alloc",
-    "mvs_host_free", "mvs_view_partition", "mvs_frame_create", "mvs_frame_destroy", "mvs_frame_upload",
+    "mvs_host_free", "mvs_view_partition", "mvs_exchange_plan", "mvs_frame_create", "mvs_frame_destroy", "mvs_frame_upload",
     "mvs_frame_download", "mvs_frame_upload_async", "mvs_frame_download_async", "mvs_frame_dev_ptr",
     "mvs_frame_sizes", "mvs_frame_slic", "mvs_frame_block_match", "mvs_frame_refine", "mvs_frame_flatness",
     "mvs_frame_init_state", "mvs_frame_propagate", "mvs_frame_fusion", "mvs_frame_run", "mvs_frame_exchange",
@@ -45,7 +45,7 @@ def lib():
             raise MvsError(
                 f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                 "(nvcc, sm_100a).  There is no CPU fallback.")
-        _lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+        _lib = C.CDLL(LIB_PATH)
         _lib.mvs_last_error.restype = C.c_char_p
         for s in SYMBOLS:
             if s != "mvs_last_error":

@@ -138,6 +138,17 @@ def view_partition(V, nranks, rank):
     return lo.value, hi.value
 
 
+def exchange_plan(V, nranks, subset, subset_num):
+    """the halo transfers mvs_frame_exchange issues: list of (view, source rank, destination rank)"""
+    subset = np.ascontiguousarray(subset, np.int32)
+    subset_num = np.ascontiguousarray(subset_num, np.int32)
+    n = C.c_int()
+    check(lib().mvs_exchange_plan(int(V), int(nranks), _ptr(subset), _ptr(subset_num), None, 0, C.byref(n)))
+    t = np.zeros((max(n.value, 1), 3), np.int32)
+    check(lib().mvs_exchange_plan(int(V), int(nranks), _ptr(subset), _ptr(subset_num), _ptr(t), n.value, C.byref(n)))
+    return [tuple(int(x) for x in row) for row in t[:n.value]]
+
+
 class PinnedBuffer:
     """page-locked host memory (cudaHostAlloc) exposed as a numpy array"""
 

@@ -38,7 +38,7 @@ def build_native(force=False, verbose=False):
     cu = [os.path.join(CSRC, f) for f in ("slic.cu", "photo.cu", "refine.cu", "propagate.cu", "capi.cu")]
     deps = cu + [os.path.join(CSRC, f) for f in ("common.cuh", "mvs_math.cuh")] + [os.path.join(ROOT, "include", "mvs_capi.h")]
     if force or _newer(LIB, deps):
-        cmd = [_nvcc()] + NVCC_FLAGS + ["-shared", "-o", LIB] + cu + ["-lnccl"]
+        cmd = [_nvcc()] + NVCC_FLAGS + ["-shared", "-o", LIB] + cu + ["-ldl"]
         if verbose:
             print(" ".join(cmd))
         subprocess.check_call(cmd)

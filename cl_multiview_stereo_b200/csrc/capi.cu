@@ -8,7 +8,8 @@
 // the buffer fusion reads).
 #include "../../include/mvs_capi.h"
 #include "common.cuh"
-#include <nccl.h>
+#include <nccl.h>   // types and prototypes only: the library is bound at run time (below)
+#include <dlfcn.h>
 #include <math.h>
 #include <stdio.h>
 #include <stdarg.h>
@@ -38,11 +39,48 @@ static int fail(const char *fmt, ...)
         if (e_ != cudaSuccess) return fail("%s:%d CUDA error %d (%s) in %s", __FILE__, __LINE__, (int)e_,  \
                                            cudaGetErrorString(e_), #call);                                  \
     } while (0)
+// NCCL is bound at run time, not at link time: a host process may already carry its own NCCL
+// (PyTorch bundles one), and two different NCCL builds in one address space do not mix.  The
+// copy that is already loaded wins (RTLD_NOLOAD); otherwise the system library is opened.
+// Single-GPU use never touches NCCL.
+struct NcclApi {
+    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+    decltype(&ncclCommInitRank) CommInitRank = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+    decltype(&ncclGroupStart) GroupStart = nullptr;
+    decltype(&ncclGroupEnd) GroupEnd = nullptr;
+    decltype(&ncclSend) Send = nullptr;
+    decltype(&ncclRecv) Recv = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
+    void *handle = nullptr;
+    bool ok = false;
+};
+static NcclApi g_nccl;
+
+static int nccl_bind()
+{
+    if (g_nccl.ok) return 0;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
+    if (!h) return fail("NCCL is not available: %s", dlerror());
+    g_nccl.handle = h;
+#define BIND(name)                                                                  \
+    g_nccl.name = (decltype(g_nccl.name))dlsym(h, "nccl" #name);                    \
+    if (!g_nccl.name) return fail("libnccl lacks nccl" #name)
+    BIND(GetUniqueId); BIND(CommInitRank); BIND(CommDestroy); BIND(GetErrorString);
+    BIND(GroupStart); BIND(GroupEnd); BIND(Send); BIND(Recv); BIND(AllGather);
+#undef BIND
+    g_nccl.ok = true;
+    return 0;
+}
+
 #define NK(call)                                                                                            \
     do {                                                                                                    \
-        ncclResult_t r_ = (call);                                                                           \
-        if (r_ != ncclSuccess) return fail("%s:%d NCCL error %d (%s) in %s", __FILE__, __LINE__, (int)r_,  \
-                                           ncclGetErrorString(r_), #call);                                  \
+        ncclResult_t r_ = (g_nccl.call);                                                                    \
+        if (r_ != ncclSuccess) return fail("%s:%d NCCL error %d (%s) in nccl%s", __FILE__, __LINE__, (int)r_, \
+                                           g_nccl.GetErrorString(r_), #call);                               \
     } while (0)
 
 struct mvs_ctx {
@@ -101,7 +139,7 @@ extern "C" int mvs_ctx_destroy(mvs_ctx *c)
 {
     if (!c) return 0;
     cudaSetDevice(c->device);
-    if (c->comm) ncclCommDestroy(c->comm);
+    if (c->comm && g_nccl.ok) g_nccl.CommDestroy(c->comm);
     for (cudaEvent_t e : c->user_ev) if (e) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -152,7 +190,8 @@ extern "C" int mvs_ctx_event_elapsed(mvs_ctx *c, int a, int b, float *ms)
 extern "C" int mvs_comm_unique_id(void *id128)
 {
     static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
-    NK(ncclGetUniqueId((ncclUniqueId *)id128));
+    if (nccl_bind()) return 1;
+    NK(GetUniqueId((ncclUniqueId *)id128));
     return 0;
 }
 
@@ -162,7 +201,8 @@ extern "C" int mvs_comm_init(mvs_ctx *c, const void *id128, int nranks, int rank
     CK(cudaSetDevice(c->device));
     ncclUniqueId id;
     memcpy(&id, id128, sizeof id);
-    NK(ncclCommInitRank(&c->comm, nranks, id, rank));
+    if (nccl_bind()) return 1;
+    NK(CommInitRank(&c->comm, nranks, id, rank));
     c->nranks = nranks;
     c->rank = rank;
     return 0;
@@ -463,28 +503,56 @@ static int check_launch(const char *what)
 // ---- multi-GPU halo exchange ---------------------------------------------------------------
 // Rank r needs view v when v is a neighbour (view_subset) of one of r's own views.  Every
 // rank derives the same global plan; transfers are grouped ncclSend/ncclRecv over NVLink.
-static int exchange_raw(mvs_frame *f, char *base, size_t per_view)
+// The plan is a pure host function of (V, nranks, neighbour lists) so that it can be tested
+// without a GPU: transfers (view, src rank, dst rank) in issue order.
+static void build_exchange_plan(int V, int n, const int *subset, const int *subset_num, std::vector<int> &triples)
 {
-    mvs_ctx *c = f->ctx;
-    if (!c->comm || c->nranks == 1) return 0;
-    int V = f->d.V, n = c->nranks;
     std::vector<int> lo(n), hi(n), owner(V);
     for (int r = 0; r < n; ++r) {
         mvs_view_partition(V, n, r, &lo[r], &hi[r]);
         for (int v = lo[r]; v < hi[r]; ++v) owner[v] = r;
     }
-    NK(ncclGroupStart());
     for (int r = 0; r < n; ++r) {
         std::vector<char> need(V, 0);
         for (int u = lo[r]; u < hi[r]; ++u)
-            for (int k = 0; k < f->h_subset_num[u]; ++k) need[f->h_subset[(size_t)u * V + k]] = 1;
-        for (int v = 0; v < V; ++v) {
-            if (!need[v] || owner[v] == r) continue;
-            if (owner[v] == c->rank) NK(ncclSend(base + per_view * v, per_view, ncclChar, r, c->comm, c->stream));
-            if (r == c->rank) NK(ncclRecv(base + per_view * v, per_view, ncclChar, owner[v], c->comm, c->stream));
-        }
+            for (int k = 0; k < subset_num[u]; ++k) need[subset[(size_t)u * V + k]] = 1;
+        for (int v = 0; v < V; ++v)
+            if (need[v] && owner[v] != r) { triples.push_back(v); triples.push_back(owner[v]); triples.push_back(r); }
     }
-    NK(ncclGroupEnd());
+}
+
+extern "C" int mvs_exchange_plan(int V, int nranks, const int *view_subset, const int *subset_num, int *triples, int cap,
+                                 int *count)
+{
+    if (V <= 0 || nranks <= 0 || !view_subset || !subset_num || !count) return fail("mvs_exchange_plan: bad argument");
+    for (int z = 0; z < V; ++z) {
+        if (subset_num[z] < 0 || subset_num[z] > V) return fail("subset_num[%d]=%d out of range", z, subset_num[z]);
+        for (int k = 0; k < subset_num[z]; ++k)
+            if (view_subset[z * V + k] < 0 || view_subset[z * V + k] >= V) return fail("view_subset[%d][%d] out of range", z, k);
+    }
+    std::vector<int> t;
+    build_exchange_plan(V, nranks, view_subset, subset_num, t);
+    *count = (int)t.size() / 3;
+    if (triples) {
+        if (cap < *count) return fail("mvs_exchange_plan: %d transfers, room for %d", *count, cap);
+        memcpy(triples, t.data(), sizeof(int) * t.size());
+    }
+    return 0;
+}
+
+static int exchange_raw(mvs_frame *f, char *base, size_t per_view)
+{
+    mvs_ctx *c = f->ctx;
+    if (!c->comm || c->nranks == 1) return 0;
+    std::vector<int> t;
+    build_exchange_plan(f->d.V, c->nranks, f->h_subset.data(), f->h_subset_num.data(), t);
+    NK(GroupStart());
+    for (size_t i = 0; i + 2 < t.size(); i += 3) {
+        const int v = t[i], src = t[i + 1], dst = t[i + 2];
+        if (src == c->rank) NK(Send(base + per_view * v, per_view, ncclChar, dst, c->comm, c->stream));
+        if (dst == c->rank) NK(Recv(base + per_view * v, per_view, ncclChar, src, c->comm, c->stream));
+    }
+    NK(GroupEnd());
     return 0;
 }
 

@@ -84,6 +84,11 @@ int mvs_comm_unique_id(void *id128);
 int mvs_comm_init(mvs_ctx *ctx, const void *id128, int nranks, int rank);
 /* contiguous partition of V views over nranks (the plan mvs_frame_exchange assumes) */
 int mvs_view_partition(int V, int nranks, int rank, int *lo, int *hi);
+/* the halo plan mvs_frame_exchange follows (pure host code, no device needed): every transfer
+ * {view, source rank, destination rank} in issue order, for the neighbour lists the reference
+ * builds at pipeline.cpp:121-142.  triples may be NULL to query *count only. */
+int mvs_exchange_plan(int V, int nranks, const int *view_subset, const int *subset_num, int *triples, int cap,
+                      int *count);
 
 /* ---- frame: device-resident pipeline over V = array_width*array_height views ---- */
 /* view_lo..view_hi-1 are the views this context computes (all views for single GPU);
