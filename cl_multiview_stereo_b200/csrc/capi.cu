@@ -277,6 +277,12 @@ static int set_tables(mvs_frame *f, const int *subset, const int *subset_num, co
         for (int k = 0; k < subset_num[z]; ++k)
             if (subset[z * V + k] < 0 || subset[z * V + k] >= V) return fail("view_subset[%d][%d] out of range", z, k);
     }
+    f->d.unit_baseline = 1;
+    for (int z = 0; z < V; ++z)
+        for (int k = 0; k < subset_num[z]; ++k) {
+            const int v = subset[z * V + k], aw = f->d.aw;
+            if (abs(v % aw - z % aw) > 1 || abs(v / aw - z / aw) > 1) f->d.unit_baseline = 0;
+        }
     cudaStream_t st = f->ctx->stream;
     CK(cudaMemcpyAsync(f->d.view_subset, f->h_subset.data(), sizeof(int) * V * V, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(f->d.subset_num, f->h_subset_num.data(), sizeof(int) * V, cudaMemcpyHostToDevice, st));

@@ -25,6 +25,7 @@ struct FrameDev {
     int *subset_num;    // [V]
     float *levels;      // [L]
     int num_levels;
+    int unit_baseline;  // every neighbour view at most one camera apart in x and y
 };
 
 struct SlicArgs {

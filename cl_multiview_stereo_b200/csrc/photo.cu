@@ -53,26 +53,35 @@ int launch_boundary(const FrameDev &f, int z0, int z1, cudaStream_t st)
 }
 
 // ---------------------------------------------------------------------------------------
-// Block matching.  One WARP per superpixel, lanes over disparity levels (31 levels at the
-// shipped settings fill a warp; more levels loop in chunks of 32).  The 25 reference
-// samples of the superpixel (positions + Lab) are level- and view-invariant: they are
-// staged once per warp in shared memory and read back as warp-wide broadcasts.  For a
-// neighbouring view in the same camera row, consecutive levels project to consecutive
-// pixels, so a warp-wide gather of the projected Lab is one contiguous 512-byte segment.
-// Cost accumulation order is the reference's: per (level, view) a sequential float sum
-// over i (x) outer / j (y) inner with the '+30, -30' sequence (clcode.cl:1030-1053);
+// Block matching.  One WARP per superpixel.  The 25 reference samples of the superpixel
+// (positions + Lab) are level- and view-invariant: staged once per warp in shared memory.
+//
+// The kernel is bound by the L1 tag stage (one cycle per distinct 128-byte line a warp-wide
+// gather touches), so the lane mapping of the gather follows the geometry of the pair:
+//  * neighbour in the same camera row (dy = 0): lanes = disparity levels.  Consecutive levels
+//    project to consecutive pixels of ONE image row: a warp-wide gather is one contiguous
+//    512-byte segment (4-5 lines).
+//  * neighbour in another camera row: levels land on 32 different image rows (32 lines per
+//    gather with lanes = levels).  Here the lanes run over (level, x-sample) instead, so that
+//    the five x-samples of a sample row share a line (6-10 lines per gather); the per-sample
+//    terms are staged in shared memory and the cost chain is then run with lanes = levels.
+// Cost accumulation order is the reference's in both forms: per (level, view) a sequential
+// float sum over i (x) outer / j (y) inner with the '+30, -30' sequence (clcode.cl:1030-1053);
 // min over views and argmin over levels use strict '<' (first view / lowest level wins,
 // clcode.cl:1054-1063); the cross-lane argmin breaks ties toward the lower level.
 // ---------------------------------------------------------------------------------------
 constexpr int BM_WARPS = 8;
+constexpr float BM_OUTSIDE = -1.0f;   // staged term of a sample that projects outside (terms are >= 0 or NaN)
 
-__global__ void __launch_bounds__(BM_WARPS * 32)
+__global__ void __launch_bounds__(BM_WARPS * 32, 5)
 k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const uint2 *__restrict__ rep,
               const float *__restrict__ levels, int disp_num, const int *__restrict__ view_subset,
               const int *__restrict__ subset_num, int aw, int V, int W, int H, int N, int M, float bl_ratio, int z0)
 {
-    __shared__ float4 s_ref[BM_WARPS][25];   // Lab of the reference samples
-    __shared__ int2 s_xy[BM_WARPS][25];      // their pixel coordinates (x = -1 marks "outside")
+    __shared__ float4 s_ref[BM_WARPS][25];      // Lab of the reference samples
+    __shared__ float2 s_xy[BM_WARPS][25];       // their pixel coordinates as floats (exact below 2^24)
+    __shared__ float s_t[BM_WARPS][32 * 25];    // per (level, sample) cost terms of the current pair
+    const unsigned FULL = 0xffffffffu;
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int sp = blockIdx.x * BM_WARPS + warp;
     int z = z0 + blockIdx.y;
@@ -89,20 +98,24 @@ k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const ui
     float4 m0 = map[2 * mi];
     float cxf = m0.y, cyf = m0.z;
     const float4 *ref_img = lab + (size_t)z * N;
+    bool ref_ok = false;
     if (lane < 25) {
         int i = lane / 5 - 2, j = lane % 5 - 2;
         int xr = f2i(cxf + (float)i * stepx);
         int yr = f2i(cyf + (float)j * stepy);
-        bool ok = xr >= 0 && yr >= 0 && xr < W && yr < H;
-        s_xy[warp][lane] = make_int2(ok ? xr : -1, yr);
-        s_ref[warp][lane] = ok ? ref_img[(size_t)yr * W + xr] : make_float4(0, 0, 0, 0);
+        ref_ok = xr >= 0 && yr >= 0 && xr < W && yr < H;
+        s_xy[warp][lane] = ref_ok ? make_float2((float)xr, (float)yr) : make_float2(0.0f, 0.0f);
+        s_ref[warp][lane] = ref_ok ? ref_img[(size_t)yr * W + xr] : make_float4(0, 0, 0, 0);
     }
+    const unsigned vmask = __ballot_sync(FULL, ref_ok);   // bit s: reference sample s lies inside the image
     __syncwarp();
 
     int refx = z % aw, refy = z / aw;
     int ns = subset_num[z];
     float cost_est = 1000000.0f, disp_est = 0.0f;
+    float *t = s_t[warp];
     for (int base = 0; base < disp_num; base += 32) {
+        const int nlev = min(32, disp_num - base);
         int dl = base + lane;
         bool active = dl < disp_num;
         float d = active ? levels[dl] : 0.0f;
@@ -111,21 +124,56 @@ k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const ui
         for (int n = 0; n < ns; n++) {
             int view = view_subset[V * z + n];
             float dx = (float)(view % aw - refx), dy = (float)(view / aw - refy);
-            float sx = d * dx, sy = bd * dy;
             const float4 *pimg = lab + (size_t)view * N;
             float val = 0.0f;
-#pragma unroll 5
-            for (int s = 0; s < 25; ++s) {
-                int2 xy = s_xy[warp][s];
-                int xp = f2i((float)xy.x - sx);
-                int yp = f2i((float)xy.y - sy);
-                val += 30.0f;
-                if (xy.x >= 0 && xp >= 0 && yp >= 0 && xp < W && yp < H) {
-                    val -= 30.0f;
-                    float4 cr = s_ref[warp][s];
-                    float4 cp = pimg[(size_t)yp * W + xp];
-                    val += fabsf(cr.x - cp.x) + fabsf(cr.y - cp.y) + fabsf(cr.z - cp.z);
+            if (dy == 0.0f) {
+                float sx = d * dx, sy = bd * dy;
+#pragma unroll
+                for (int s = 0; s < 25; ++s) {
+                    float2 xy = s_xy[warp][s];
+                    int xp = f2i(xy.x - sx);
+                    int yp = f2i(xy.y - sy);
+                    val += 30.0f;
+                    if (((vmask >> s) & 1u) && (unsigned)xp < (unsigned)W && (unsigned)yp < (unsigned)H) {
+                        val -= 30.0f;
+                        float4 cr = s_ref[warp][s];
+                        float4 cp = pimg[yp * W + xp];
+                        val += fabsf(cr.x - cp.x) + fabsf(cr.y - cp.y) + fabsf(cr.z - cp.z);
+                    }
                 }
+            } else {
+                // gather with lanes over (level, x-sample); j = sample row (uniform per pass)
+#pragma unroll 1
+                for (int j = 0; j < 5; ++j) {
+#pragma unroll
+                    for (int rr = 0; rr < 5; ++rr) {   // nlev * 5 <= 160 items per sample row
+                        const int e = rr * 32 + lane;
+                        const bool item = e < nlev * 5;
+                        const int l = item ? e / 5 : 0, i = e - 5 * l;
+                        const int s = item ? i * 5 + j : 0;
+                        const float dd = __shfl_sync(FULL, d, l);
+                        const float2 xy = s_xy[warp][s];
+                        const int xp = f2i(xy.x - dd * dx);
+                        const int yp = f2i(xy.y - (bl_ratio * dd) * dy);
+                        float tv = BM_OUTSIDE;
+                        if (item && ((vmask >> s) & 1u) && (unsigned)xp < (unsigned)W && (unsigned)yp < (unsigned)H) {
+                            const float4 cr = s_ref[warp][s];
+                            const float4 cp = pimg[yp * W + xp];
+                            tv = fabsf(cr.x - cp.x) + fabsf(cr.y - cp.y) + fabsf(cr.z - cp.z);
+                        }
+                        if (item) t[l * 25 + s] = tv;
+                    }
+                }
+                __syncwarp();
+                if (active) {
+#pragma unroll
+                    for (int s = 0; s < 25; ++s) {
+                        const float tv = t[lane * 25 + s];
+                        val += 30.0f;
+                        if (!(tv == BM_OUTSIDE)) { val -= 30.0f; val += tv; }
+                    }
+                }
+                __syncwarp();
             }
             if (val < min_val) min_val = val;
         }
@@ -134,8 +182,8 @@ k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const ui
         int bi = dl;
 #pragma unroll
         for (int o = 16; o >= 1; o >>= 1) {
-            float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            float ov = __shfl_xor_sync(FULL, bv, o);
+            int oi = __shfl_xor_sync(FULL, bi, o);
             if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
         }
         if (bv < cost_est) { cost_est = bv; disp_est = levels[bi]; }

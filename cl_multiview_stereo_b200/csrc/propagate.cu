@@ -4,23 +4,31 @@
 // helpers update (:1635-1673), spatialRefinement (:1687-1723), compute_smoothness
 // (:1407-1525), compute_consistency (:1528-1631) and cross_product_test (:1676-1685).
 //
-// Mapping.  The reference runs one work-item per superpixel and evaluates its 16+ candidate
-// planes one after another; each evaluation is ~70 reprojected samples (9 samples x up to 8
-// neighbour views, three dependent gathers each) plus 8..60 smoothness terms.  Here EIGHT
-// lanes (an "octet") share one superpixel: the (view, sample) items and the smoothness terms
-// of a candidate are spread over the octet, so eight gather chains are in flight per
-// superpixel, registers per thread stay low and there is ONE copy of the evaluation code
-// (the one-thread-per-superpixel form inlines it at every call site: 18k SASS instructions,
-// stalled on instruction fetch).  A CTA is 4 warps = a 4x4 tile of superpixels.
+// What the reference does per superpixel: a sequential greedy walk over 16+ candidate planes
+// (8 neighbours, up to 4K far neighbours, 8 planes through neighbour pairs); every candidate
+// costs ~70 reprojected samples (9 samples x up to 8 neighbour views, dependent gathers) plus
+// 8..60 smoothness terms, and is then accepted or not against the running best.
 //
-// Bit-exactness.  Every float sum of the reference is a sequential chain in a fixed order;
-// the octet computes the addends in parallel, stages them in shared memory and adds them in
-// the reference's order (samples k = 0..8 inside a view, views in subset order, smoothness
-// terms near-then-far).  Candidate-invariant factors (colour similarity of a smoothness
-// term, centre offsets, the neighbour's disparity, the weight norm) are computed once per
-// superpixel instead of once per candidate -- same operations, same operands, same bits.
+// What this kernel does instead (same results, bit for bit):
+//  * EIGHT lanes (an "octet") share one superpixel; a CTA is 4 warps = a 4x4 tile of superpixels.
+//  * The two costs of a candidate are a pure function of its plane (d, n) for the fixed input
+//    state, and the candidate planes of the first two groups do not depend on the running best.
+//    So the octet first GENERATES all neighbour / far-neighbour planes in parallel (one lane per
+//    candidate), removes bit-identical duplicates (neighbouring superpixels often carry the same
+//    plane), EVALUATES the unique planes in batches, and only then replays the reference's
+//    sequential acceptance chain from the table of costs.  The pair planes keep d (clcode.cl:1716),
+//    so all eight depend only on the d left by that chain: one more generate / dedup / evaluate /
+//    replay round.
+//  * Inside a batch the work is spread so that every float sum of the reference stays a
+//    sequential chain in one lane, in the reference's order: a lane owns one (plane, neighbour
+//    view) pair and walks its 9 samples in order; smoothness products are computed across the
+//    octet, staged in shared memory and added in order by the lane that owns the plane.
+//  * Candidate-invariant factors (colour similarity of a smoothness term, centre offsets, the
+//    neighbour's disparity, the weight norm) are computed once per superpixel instead of once
+//    per candidate -- same operations, same operands, same bits.
 #include "common.cuh"
 #include "mvs_math.cuh"
+#include <stdlib.h>
 
 namespace mvs {
 
@@ -29,25 +37,7 @@ namespace {
 constexpr int PR_WARPS = 4;                 // warps per CTA (tile rows)
 constexpr int PR_OCT = 4;                   // octets per warp (tile columns)
 constexpr int PR_SPB = PR_WARPS * PR_OCT;   // superpixels per CTA
-constexpr int PR_ITEMS = 72;                // 9 samples x 8 neighbour views at most
-
-// shared-memory record of one superpixel (dynamic: tab/prod hold tmax entries)
-constexpr int PR_MEMO = 4;                  // evaluated planes remembered per superpixel
-
-struct SpShared {
-    float4 samp[9];          // {sx, sy (integers held as float), cx - sx, cy - sy}
-    float4 viewt[8];         // {view * N (int bits), dvx, dvy, view * M (int bits)}
-    float2 item[PR_ITEMS];   // per (view, sample): {visible term or flag, visibility term or -1}
-    float2 di[10];           // per sample of the current candidate: {d_intrp, bl_ratio * d_intrp}
-    float4 memo_plane[PR_MEMO];   // {d, nx, ny, nz} of the last evaluated candidates
-    float2 memo_cost[PR_MEMO];    // their {smoothness, consistency}
-};
-static_assert(sizeof(SpShared) % 16 == 0, "SpShared must keep float4 alignment");
-
-__host__ __device__ inline size_t sp_shared_bytes(int tmax)
-{
-    return sizeof(SpShared) + (size_t)tmax * (sizeof(float4) + sizeof(float));
-}
+constexpr int PR_UB = 4;                    // unique planes evaluated per batch
 
 struct PArgs {
     const float4 *map;        // [V][M][2]
@@ -63,8 +53,32 @@ struct PArgs {
     float gamma, alpha, bl_ratio, fuse;
     int K;                    // no_kernel_steps of this iteration
     float kernel_step_size;
-    int iter, z0, tmax;
+    int iter, z0;
+    int tmax;                 // smoothness terms per superpixel at most (8 + 4K)
+    int ncmax;                // candidate slots per superpixel at most (valid neighbours + far + 8 pairs)
 };
+
+// shared-memory record of one superpixel (dynamic part sized by tmax / ncmax)
+struct SpLayout {
+    int tab, cp, cc, cw, own, uniq, sres, stage, total;
+};
+
+__host__ __device__ inline SpLayout sp_layout(int tmax, int ncmax)
+{
+    SpLayout L;
+    int o = 9 * 16 + 8 * 16;                  // samp[9], viewt[8]
+    L.tab = o;   o += 16 * tmax;              // float4 tab[tmax]
+    L.cp = o;    o += 16 * ncmax;             // float4 candidate planes
+    L.cc = o;    o += 8 * ncmax;              // float2 costs of the unique ones
+    L.sres = o;  o += 8 * PR_UB * 8;          // float2 per (plane, view): {term, flags}
+    const int prod_bytes = 4 * PR_UB * (tmax + 1), sdi_bytes = 16 * PR_UB * 9;
+    L.stage = o; o += ((prod_bytes > sdi_bytes ? prod_bytes : sdi_bytes) + 15) & ~15;   // sdi (E,F) then prod (G,H)
+    L.cw = o;    o += 4 * ncmax;              // float acceptance weight (colour similarity to the source)
+    L.own = o;   o += ncmax;                  // u8: slot whose costs this candidate takes
+    L.uniq = o;  o += ncmax;                  // u8: slots of the unique planes, in order
+    L.total = (o + 15) & ~15;
+    return L;
+}
 
 // in-range test + linear index of the map cell (x, y)
 __device__ __forceinline__ bool cell(const PArgs &a, int x, int y, int &q)
@@ -82,33 +96,41 @@ __device__ __forceinline__ void near_offset(int s, int &i, int &j)
     j = t % 3 - 1;
 }
 
-// acceptance test shared by update() and spatialRefinement() (clcode.cl:1663-1669,
-// 1713-1718): update() weighs sm1 by the colour similarity to the source neighbour,
-// spatialRefinement() does not (wsim = 1, exact) and keeps d (its cd IS the current d)
-__device__ __forceinline__ void accept(int iter, bool, float sm1, float cs1, float wsim, float cd, float cnx,
-                                       float cny, float cnz, float &pd, float &pnx, float &pny, float &pnz,
-                                       float &psm, float &pcs)
+__device__ __forceinline__ bool same_bits(const float4 &p, const float4 &q)
 {
-    if ((iter < 4 && sm1 * wsim > psm) || cs1 * sm1 > psm * pcs) {
-        pd = cd; psm = sm1; pcs = cs1; pnx = cnx; pny = cny; pnz = cnz;
-    }
+    return __float_as_int(p.x) == __float_as_int(q.x) && __float_as_int(p.y) == __float_as_int(q.y) &&
+           __float_as_int(p.z) == __float_as_int(q.z) && __float_as_int(p.w) == __float_as_int(q.w);
 }
 
 } // namespace
 
-__global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
+// UNIT: every neighbour view is at most one camera apart in x and y (neib_hor, neib_ver <= 1).
+// Then round(d * dv) == dv * round(d) exactly (dv in {-1, 0, 1}; holds for inf / NaN too), and
+// the two rounds of a sample are taken once per (plane, sample) instead of once per view.
+template <bool UNIT, int MINB>
+__global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
 {
     extern __shared__ __align__(16) unsigned char pr_smem[];
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int l8 = lane & 7, obase = lane & 24;
+    const unsigned lower8 = (1u << l8) - 1u;
     const int x = blockIdx.x * PR_OCT + (lane >> 3), y = blockIdx.y * PR_WARPS + warp, z = a.z0 + blockIdx.z;
     const bool live = x < a.mw && y < a.mh;
 
-    unsigned char *sbase = pr_smem + (size_t)(warp * PR_OCT + (lane >> 3)) * sp_shared_bytes(a.tmax);
-    SpShared *sh = reinterpret_cast<SpShared *>(sbase);
-    float4 *tab = reinterpret_cast<float4 *>(sbase + sizeof(SpShared));   // {cx-cxq, cy-cyq, d_q, similarity}
-    float *prod = reinterpret_cast<float *>(tab + a.tmax);
+    const SpLayout L = sp_layout(a.tmax, a.ncmax);
+    unsigned char *sbase = pr_smem + (size_t)(warp * PR_OCT + (lane >> 3)) * L.total;
+    float4 *samp = reinterpret_cast<float4 *>(sbase);            // {sx, sy (integers held as float), cx - sx, cy - sy}
+    float4 *viewt = samp + 9;                                    // {view * N (int bits), dvx, dvy, view * M (int bits)}
+    float4 *tab = reinterpret_cast<float4 *>(sbase + L.tab);     // {cx-cxq, cy-cyq, d_q, similarity}
+    float4 *cp = reinterpret_cast<float4 *>(sbase + L.cp);       // candidate planes {d, nx, ny, nz}
+    float2 *cc = reinterpret_cast<float2 *>(sbase + L.cc);       // {smoothness, consistency}
+    float *cw = reinterpret_cast<float *>(sbase + L.cw);
+    unsigned char *own = sbase + L.own, *uniq = sbase + L.uniq;
+    float2 *sres = reinterpret_cast<float2 *>(sbase + L.sres);
+    float4 *sdi = reinterpret_cast<float4 *>(sbase + L.stage);   // per (plane, sample): {d_intrp, bl*d_intrp, round, round}
+    float *prod = reinterpret_cast<float *>(sbase + L.stage);    // per (plane, term), row stride tmax + 1
+    const int pstride = a.tmax + 1;
 
     const size_t zM = (size_t)z * a.M;
     const float4 *vm = a.map + 2 * zM;
@@ -119,9 +141,10 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
     const float4 ma = vm[2 * sp], mb = vm[2 * sp + 1];
     const float cx = ma.y, cy = ma.z, cL = ma.w, ca = mb.x, cb = mb.y;
     const float2 fl = a.flat[zM + sp];
-    const int ns = a.subset_num[z];
+    const int ns = live ? a.subset_num[z] : 0;
     const int camx = z % a.aw, camy = z / a.aw;
     const double half_fly = 0.5 * (double)fl.y;   // clcode.cl:1621 is a double expression
+    const unsigned ns_inv = 65536u / (unsigned)max(ns, 1) + 1u;   // p / ns for p < 64
 
     // sample table: sample k = (i+1)*3 + (j+1) sits s_k pixels along ray (i, j) from the
     // truncated centre (clcode.cl:1547-1566); rep bytes are {nw,w,sw,n,s,ne,e,se}
@@ -133,12 +156,12 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
             int s = k == 4 ? 0 : (int)((r64 >> (8 * (k < 4 ? k : k - 1))) & 255);
             int sx = icx + s * (k / 3 - 1), sy = icy + s * (k % 3 - 1);
             // |sx|, |sy| < 2^24: the float copies are exact
-            sh->samp[k] = make_float4((float)sx, (float)sy, cx - (float)sx, cy - (float)sy);
+            samp[k] = make_float4((float)sx, (float)sy, cx - (float)sx, cy - (float)sy);
         }
         if (l8 < ns) {
             int view = a.view_subset[a.V * z + l8];
-            sh->viewt[l8] = make_float4(__int_as_float(view * a.N), (float)(view % a.aw - camx),
-                                        (float)(view / a.aw - camy), __int_as_float(view * a.M));
+            viewt[l8] = make_float4(__int_as_float(view * a.N), (float)(view % a.aw - camx),
+                                    (float)(view / a.aw - camy), __int_as_float(view * a.M));
         }
     }
 
@@ -175,14 +198,195 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
                 const float4 qa = vm[2 * q], qb = vm[2 * q + 1];
                 const float diff = dist3(cL, ca, cb, qa.w, qb.x, qb.y);
                 const float sim = expf_pinned(-diff * diff * g);
-                tab[T + __popc(m8 & ((1u << l8) - 1u))] = make_float4(cx - qa.y, cy - qa.z, vp[q].x, sim);
+                tab[T + __popc(m8 & lower8)] = make_float4(cx - qa.y, cy - qa.z, vp[q].x, sim);
             }
             T += __popc(m8);
         }
     }
+
+    // ---- candidate planes of update(): neighbours, then far neighbours (clcode.cl:1768-1850) ----
+    // slot s: 0..7 near neighbours (x offset outer); 8 + 4(i-1) + {0,1,2,3} = UP, DOWN, LEFT, RIGHT
+    // at i * (int)kernel_step_size.  One lane per slot; valid ones are compacted in order.
+    int NU = 0;
+    {
+        const int stride = f2i(a.kernel_step_size);
+        const bool far_possible = stride < max(a.mw, a.mh);
+        const int nslots = far_possible ? 8 + 4 * a.K : 8;
+        for (int s0 = 0; s0 < nslots; s0 += 8) {
+            const int s = s0 + l8;
+            bool ok = false;
+            int q1 = 0;
+            if (live && s < nslots) {
+                if (s < 8) {
+                    int i, j;
+                    near_offset(s, i, j);
+                    ok = cell(a, x + i, y + j, q1);
+                } else {
+                    const int off = (1 + ((s - 8) >> 2)) * stride, dir = (s - 8) & 3;
+                    if (dir == 0) { ok = y > off; q1 = a.mw * (y - (off + 1)) + x; }
+                    else if (dir == 1) { ok = y < a.mh - off - 1; q1 = a.mw * (y + off + 1) + x; }
+                    else if (dir == 2) { ok = x > off; q1 = a.mw * y + x - off - 1; }
+                    else { ok = x < a.mw - off - 1; q1 = a.mw * y + x + off + 1; }
+                }
+            }
+            const unsigned m8 = (__ballot_sync(FULL, ok) >> obase) & 255u;
+            if (ok) {   // neighbour's plane extrapolated to the own centre (clcode.cl:1643-1651)
+                const float4 pl = vp[q1];
+                const float4 qa = vm[2 * q1], qb = vm[2 * q1 + 1];
+                const float cd = (pl.y * (qa.y - cx) + pl.z * (qa.z - cy) + pl.w * pl.x) / pl.w;
+                const float diff = dist3(cL, ca, cb, qa.w, qb.x, qb.y);
+                const int pos = NU + __popc(m8 & lower8);
+                cp[pos] = make_float4(cd, pl.y, pl.z, pl.w);
+                cw[pos] = expf_pinned(-diff * diff * a.gamma);
+            }
+            NU += __popc(m8);
+        }
+    }
     __syncwarp();
+
     float weight_norm = 0.0f;
     for (int t = 0; t < T; ++t) weight_norm += tab[t].w;
+
+    // ---- evaluation of the unique planes uniq[u0 .. u1) in batches of PR_UB ----
+    // (u0, u1 differ between the octets of a warp; all barriers are warp-wide)
+    auto evaluate = [&](int u0, int u1) {
+        for (int b0 = u0; __any_sync(FULL, b0 < u1); b0 += PR_UB) {
+            const int nb = min(max(u1 - b0, 0), PR_UB);
+            // E: plane disparity at the 9 samples (clcode.cl:1571-1573), once per (plane, sample)
+            for (int e = l8; e < nb * 9; e += 8) {
+                const int u = e / 9, k = e - 9 * u;
+                const float4 pl = cp[uniq[b0 + u]];
+                const float4 sv = samp[k];
+                const float di = (pl.y * sv.z + pl.z * sv.w + pl.w * pl.x) / pl.w;
+                const float bdi = a.bl_ratio * di;
+                sdi[e] = make_float4(di, bdi, round_haz(di), round_haz(bdi));
+            }
+            __syncwarp();
+            // F: compute_consistency, one lane per (plane, neighbour view), samples in order
+            for (int p = l8; p < nb * ns; p += 8) {
+                const int u = (int)(((unsigned)p * ns_inv) >> 16), n = p - u * ns;
+                const float4 vt = viewt[n];
+                const uint32_t nbase = (uint32_t)__float_as_int(vt.x), mbase = (uint32_t)__float_as_int(vt.w);
+                float num = 0.0f, vws = 0.0f, ows = 0.0f, visibility = 0.0f, visible = 0.0f;
+                // three samples at a time: their label gathers, then their centre / plane gathers, are
+                // issued together (a sample that projects outside reads pixel 0 and is masked afterwards)
+#pragma unroll 1
+                for (int k0 = 0; k0 < 9; k0 += 3) {
+                    int pix[3];
+                    float fxp[3], fyp[3], dik[3];
+                    bool inb[3];
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) {
+                        const float4 sd = sdi[u * 9 + k0 + j];
+                        const float4 sv = samp[k0 + j];
+                        int xp, yp;
+                        if (UNIT) {
+                            xp = f2i(sv.x - sd.z * vt.y);
+                            yp = f2i(sv.y - sd.w * vt.z);
+                        } else {
+                            xp = f2i(sv.x - round_haz(sd.x * vt.y));   // clcode.cl:1576-1577
+                            yp = f2i(sv.y - round_haz(sd.y * vt.z));
+                        }
+                        inb[j] = (unsigned)xp < (unsigned)a.W && (unsigned)yp < (unsigned)a.H;
+                        pix[j] = inb[j] ? yp * a.W + xp : 0;
+                        fxp[j] = (float)xp; fyp[j] = (float)yp; dik[j] = sd.x;
+                    }
+                    uint32_t vq[3];
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) vq[j] = mbase + a.idx[nbase + (uint32_t)pix[j]];
+                    float4 qa[3], pl[3];
+                    float2 qb[3];
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) {
+                        qa[j] = a.map[2 * vq[j]];
+                        qb[j] = *reinterpret_cast<const float2 *>(a.map + 2 * vq[j] + 1);
+                        pl[j] = a.plane_in[vq[j]];
+                    }
+#pragma unroll
+                    for (int j = 0; j < 3; ++j)
+                        if (inb[j]) {
+                            const float d_proj = (pl[j].y * (qa[j].y - fxp[j]) + pl[j].z * (qa[j].z - fyp[j]) + pl[j].w * pl[j].x) / pl[j].w;
+                            const float diff = d_proj - dik[j];
+                            // visible += when_visible * exp(..): 0 * exp is +0 unless diff is NaN
+                            if (fabsf(diff) < a.fuse) { visible += expf_pinned(-diff * diff * a.alpha); vws += 1.0f; }
+                            else { if (diff != diff) visible += diff; ows += 1.0f; }
+                            const float cdiff = dist3(qa[j].w, qb[j].x, qb[j].y, cL, ca, cb);
+                            visibility += expf_pinned(-cdiff * cdiff * a.gamma);
+                            num += 1.0f;
+                        }
+                }
+                float term = 0.0f;
+                int flags = 0;   // bit0: view has samples, bit1: some visible, bit2: some occluded
+                if (num > 0.0f) {
+                    flags = 1;
+                    if (vws > 0.0f) { flags |= 2; term = (vws / num) * (visibility / vws) * (visible / vws); }
+                    if (ows > 0.0f) flags |= 4;
+                }
+                sres[u * 8 + n] = make_float2(term, __int_as_float(flags));
+            }
+            __syncwarp();   // sdi is dead from here on: prod reuses its storage
+            // G: compute_smoothness products, terms spread over the octet
+            for (int u = 0; u < nb; ++u) {
+                const float4 pl = cp[uniq[b0 + u]];
+                for (int t = l8; t < T; t += 8) {
+                    const float4 e = tab[t];
+                    const float d_intrp = (pl.y * e.x + pl.z * e.y + pl.w * pl.x) / pl.w;   // clcode.cl:1426-1428
+                    const float diff = d_intrp - e.z;
+                    prod[u * pstride + t] = e.w * expf_pinned(-diff * diff * a.alpha);
+                }
+            }
+            __syncwarp();
+            // H: ordered sums, one lane per plane: views in subset order, then the smoothness terms
+            if (l8 < nb) {
+                float consistency = 0.0f;
+                int view_counter = 0;
+                for (int n = 0; n < ns; ++n) {   // clcode.cl:1614-1622
+                    const float2 rn = sres[l8 * 8 + n];
+                    const int fn = __float_as_int(rn.y);
+                    if (fn & 1) {
+                        view_counter++;
+                        if (fn & 2) consistency += rn.x;
+                        if (fn & 4) consistency = (float)((double)consistency + half_fly);
+                    }
+                }
+                const float margin = (float)0.01;
+                const float cs1 = view_counter > 0 ? fmaxf(margin, consistency / (float)view_counter) : margin;
+                float smoothness = 0.0f;
+                const float *pr = prod + l8 * pstride;
+                for (int t = 0; t < T; ++t) smoothness += pr[t];
+                const float sm1 = weight_norm > 0.0f ? smoothness / weight_norm : (float)0.000001;
+                cc[uniq[b0 + l8]] = make_float2(sm1, cs1);
+            }
+            __syncwarp();
+        }
+    };
+
+    // ---- duplicates among slots [c_lo, c_hi): own[c] = first slot with the same plane bits among the
+    // unique planes found so far and the earlier slots of the range; new unique planes are appended ----
+    int UQ = 0;
+    auto dedup = [&](int c_lo, int c_hi) {
+        for (int c0 = c_lo; __any_sync(FULL, c0 < c_hi); c0 += 8) {
+            const int c = c0 + l8;
+            const bool valid = c < c_hi;
+            int o = c;
+            if (valid) {
+                const float4 P = cp[c];
+                bool hit = false;
+                for (int k = 0; k < UQ && !hit; ++k) {
+                    const int e = uniq[k];
+                    if (same_bits(P, cp[e])) { o = e; hit = true; }
+                }
+                for (int e = c0; e < c && !hit; ++e)
+                    if (same_bits(P, cp[e])) { o = e; hit = true; }
+                own[c] = (unsigned char)o;
+            }
+            const bool isu = valid && o == c;
+            const unsigned m8 = (__ballot_sync(FULL, isu) >> obase) & 255u;
+            if (isu) uniq[UQ + __popc(m8 & lower8)] = (unsigned char)c;
+            UQ += __popc(m8);
+            __syncwarp();
+        }
+    };
 
     // ---- current plane, carried greedily through the candidates (clcode.cl:1781-1784) ----
     float pd, pnx, pny, pnz, psm, pcs;
@@ -192,60 +396,26 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
         pd = pl.x; pnx = pl.y; pny = pl.z; pnz = pl.w; psm = co.x; pcs = co.y;
     }
 
-    // candidate numbering (clcode.cl:1768-1877): 0..7 near neighbours (x offset outer);
-    // 8..8+4K-1 far neighbours UP, DOWN, LEFT, RIGHT at i * (int)kernel_step_size;
-    // then the 8 planes through consecutive neighbour pairs, ring W,NW,N,NE,E,SE,S,SW.
-    const int stride = f2i(a.kernel_step_size);
-    const int far_end = 8 + 4 * a.K, ncand = far_end + 8;
-    const bool far_possible = stride < max(a.mw, a.mh);
-    int ci = live ? 0 : ncand;
-    int nmemo = 0;   // planes evaluated so far by this octet (memo holds the last PR_MEMO)
-
-    for (;;) {
-        // ---- next candidate of this octet that still needs an evaluation ----
-        // A candidate's costs are a pure function of its plane (cd, cn) for the fixed input
-        // state, and neighbouring superpixels often carry bit-identical planes: planes already
-        // evaluated for this superpixel take their costs from the memo and go straight to the
-        // acceptance test.
-        bool act = false, pair = false;
-        float cd = 0.0f, cnx = 0.0f, cny = 0.0f, cnz = 0.0f, wsim = 1.0f;
-        while (ci < ncand && !act) {
-            const int c = ci++;
-            int q1 = 0, q2 = 0;
-            bool ok;
-            pair = false;
-            if (c < 8) {
-                int i, j;
-                near_offset(c, i, j);
-                ok = cell(a, x + i, y + j, q1);
-            } else if (c < far_end) {
-                if (!far_possible) { ci = far_end; continue; }
-                const int off = (1 + ((c - 8) >> 2)) * stride, dir = (c - 8) & 3;
-                if (dir == 0) { ok = y > off; q1 = a.mw * (y - (off + 1)) + x; }
-                else if (dir == 1) { ok = y < a.mh - off - 1; q1 = a.mw * (y + off + 1) + x; }
-                else if (dir == 2) { ok = x > off; q1 = a.mw * y + x - off - 1; }
-                else { ok = x < a.mw - off - 1; q1 = a.mw * y + x + off + 1; }
-            } else {
-                const int r = c - far_end, r2 = (r + 1) & 7;
-                // ring position r -> offset: W,NW,N,NE,E,SE,S,SW
-                const int ox1 = (r == 0 || r == 1 || r == 7) ? -1 : ((r >= 3 && r <= 5) ? 1 : 0);
-                const int oy1 = (r >= 1 && r <= 3) ? -1 : ((r >= 5) ? 1 : 0);
-                const int ox2 = (r2 == 0 || r2 == 1 || r2 == 7) ? -1 : ((r2 >= 3 && r2 <= 5) ? 1 : 0);
-                const int oy2 = (r2 >= 1 && r2 <= 3) ? -1 : ((r2 >= 5) ? 1 : 0);
-                const bool ok1 = cell(a, x + ox1, y + oy1, q1), ok2 = cell(a, x + ox2, y + oy2, q2);
-                ok = ok1 && ok2;
-                pair = true;
-            }
-            if (!ok) continue;
-            // the candidate plane (cd, cn) and its acceptance weight
-            if (!pair) {   // update(): neighbour's plane extrapolated to the own centre (clcode.cl:1643-1651)
-                const float4 pl = vp[q1];
-                const float4 qa = vm[2 * q1], qb = vm[2 * q1 + 1];
-                cd = (pl.y * (qa.y - cx) + pl.z * (qa.z - cy) + pl.w * pl.x) / pl.w;
-                cnx = pl.y; cny = pl.z; cnz = pl.w;
-                const float diff = dist3(cL, ca, cb, qa.w, qb.x, qb.y);
-                wsim = expf_pinned(-diff * diff * a.gamma);
-            } else {       // spatialRefinement(): plane through the own point and two neighbour centres
+    // ---- two rounds of dedup / evaluate / replay.  Round 0: the update() candidates generated above,
+    // accepted by clcode.cl:1663-1669.  Round 1: the spatialRefinement() candidates, the plane through
+    // the own point and two consecutive neighbour centres of the ring W,NW,N,NE,E,SE,S,SW
+    // (clcode.cl:1852-1877, 1687-1723).  That plane keeps d, so all eight follow from the d round 0
+    // left; lane r builds pair r.  Its acceptance test (clcode.cl:1713-1718) is the update() test with
+    // a weight of exactly 1 (x * 1 == x, products commute), so both rounds share the replay code. ----
+    int c_lo = 0, c_hi = NU;
+#pragma unroll 1
+    for (int round = 0; round < 2; ++round) {
+        if (round == 1) {
+            const int r = l8, r2 = (r + 1) & 7;
+            const int ox1 = (r == 0 || r == 1 || r == 7) ? -1 : ((r >= 3 && r <= 5) ? 1 : 0);
+            const int oy1 = (r >= 1 && r <= 3) ? -1 : ((r >= 5) ? 1 : 0);
+            const int ox2 = (r2 == 0 || r2 == 1 || r2 == 7) ? -1 : ((r2 >= 3 && r2 <= 5) ? 1 : 0);
+            const int oy2 = (r2 >= 1 && r2 <= 3) ? -1 : ((r2 >= 5) ? 1 : 0);
+            int q1, q2;
+            const bool ok1 = cell(a, x + ox1, y + oy1, q1), ok2 = cell(a, x + ox2, y + oy2, q2);
+            const bool ok = live && ok1 && ok2;
+            const unsigned pm8 = (__ballot_sync(FULL, ok) >> obase) & 255u;
+            if (ok) {
                 const float4 m1 = vm[2 * q1], m2 = vm[2 * q2];
                 const float ax = m1.y - cx, ay = m1.z - cy, az = vp[q1].x - pd;
                 const float bx = m2.y - cx, by = m2.z - cy, bz = vp[q2].x - pd;
@@ -253,120 +423,27 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
                 const float cry = bx * az - ax * bz;
                 const float crz = ax * by - ay * bx;
                 const float len = sqrtf(crx * crx + cry * cry + crz * crz + 0.0f * 0.0f);
-                cnx = 0.0f; cny = 0.0f; cnz = 0.0f;
+                float cnx = 0.0f, cny = 0.0f, cnz = 0.0f;
                 if (len != 0.0f) { cnx = crx / len; cny = cry / len; cnz = crz / len; }
-                cd = pd;
-                wsim = 1.0f;
+                const int pos = NU + __popc(pm8 & lower8);
+                cp[pos] = make_float4(pd, cnx, cny, cnz);
+                cw[pos] = 1.0f;
             }
-            bool hit = false;
-            for (int e = 0; e < min(nmemo, PR_MEMO) && !hit; ++e) {
-                const float4 mp = sh->memo_plane[e];
-                if (__float_as_int(mp.x) == __float_as_int(cd) && __float_as_int(mp.y) == __float_as_int(cnx) &&
-                    __float_as_int(mp.z) == __float_as_int(cny) && __float_as_int(mp.w) == __float_as_int(cnz)) {
-                    const float2 mc = sh->memo_cost[e];
-                    accept(a.iter, pair, mc.x, mc.y, wsim, cd, cnx, cny, cnz, pd, pnx, pny, pnz, psm, pcs);
-                    hit = true;
-                }
-            }
-            act = !hit;
+            c_lo = NU;
+            c_hi = NU + __popc(pm8);
+            __syncwarp();
         }
-        if (!__any_sync(FULL, act)) break;
-
-        // ---- per-sample plane disparity of the candidate (clcode.cl:1571-1573), once per sample ----
-        if (act)
-            for (int k = l8; k < 9; k += 8) {
-                const float4 sv = sh->samp[k];
-                const float di = (cnx * sv.z + cny * sv.w + cnz * cd) / cnz;
-                sh->di[k] = make_float2(di, a.bl_ratio * di);
-            }
-        __syncwarp();
-
-        if (act) {
-            // ---- compute_consistency items: (neighbour view n, sample k) spread over the octet ----
-            const int nitems = 9 * ns;
-            for (int it = l8; it < nitems; it += 8) {
-                const int n = it / 9, k = it - 9 * n;
-                const float4 sv = sh->samp[k], vt = sh->viewt[n];
-                const float2 dd = sh->di[k];
-                const int xp = f2i(sv.x - round_haz(dd.x * vt.y));   // clcode.cl:1576-1577
-                const int yp = f2i(sv.y - round_haz(dd.y * vt.z));
-                float2 out = make_float2(0.0f, -1.0f);              // -1: sample projects outside
-                if (xp >= 0 && yp >= 0 && xp < a.W && yp < a.H) {
-                    const uint32_t q = a.idx[(uint32_t)__float_as_int(vt.x) + (uint32_t)(yp * a.W + xp)];
-                    const uint32_t vq = (uint32_t)__float_as_int(vt.w) + q;
-                    const float4 qa = a.map[2 * vq], qb = a.map[2 * vq + 1];
-                    const float4 pl = a.plane_in[vq];
-                    const float d_proj = (pl.y * (qa.y - (float)xp) + pl.z * (qa.z - (float)yp) + pl.w * pl.x) / pl.w;
-                    const float diff = d_proj - dd.x;
-                    // visible: exp term; occluded: -1 (adds +0 in the reference); NaN stays NaN
-                    out.x = fabsf(diff) < a.fuse ? expf_pinned(-diff * diff * a.alpha) : (diff != diff ? diff : -1.0f);
-                    const float cdiff = dist3(qa.w, qb.x, qb.y, cL, ca, cb);
-                    out.y = expf_pinned(-cdiff * cdiff * a.gamma);
-                }
-                sh->item[it] = out;
-            }
-            // ---- compute_smoothness terms ----
-            for (int t = l8; t < T; t += 8) {
-                const float4 e = tab[t];
-                const float d_intrp = (cnx * e.x + cny * e.y + cnz * cd) / cnz;   // clcode.cl:1426-1428
-                const float diff = d_intrp - e.z;
-                prod[t] = e.w * expf_pinned(-diff * diff * a.alpha);
+        const int u_lo = UQ;
+        dedup(c_lo, c_hi);
+        evaluate(u_lo, UQ);
+        for (int c = c_lo; c < c_hi; ++c) {
+            const float2 co = cc[own[c]];
+            const float wsim = cw[c];
+            if ((a.iter < 4 && co.x * wsim > psm) || co.y * co.x > psm * pcs) {
+                const float4 pl = cp[c];
+                pd = pl.x; pnx = pl.y; pny = pl.z; pnz = pl.w; psm = co.x; pcs = co.y;
             }
         }
-        __syncwarp();
-
-        // ---- ordered sums: samples within a view (lane n), then views, then smoothness ----
-        float term = 0.0f;
-        int flags = 0;   // bit0: view has samples, bit1: some visible, bit2: some occluded
-        if (act && l8 < ns) {
-            float num = 0.0f, vws = 0.0f, ows = 0.0f, visibility = 0.0f, visible = 0.0f;
-            const float2 *iv = sh->item + 9 * l8;
-#pragma unroll
-            for (int k = 0; k < 9; ++k) {
-                const float2 v = iv[k];
-                if (!(v.y == -1.0f)) {
-                    if (v.x >= 0.0f) { visible += v.x; vws += 1.0f; }
-                    else { if (v.x != v.x) visible += v.x; ows += 1.0f; }
-                    visibility += v.y;
-                    num += 1.0f;
-                }
-            }
-            if (num > 0.0f) {
-                flags = 1;
-                if (vws > 0.0f) { flags |= 2; term = (vws / num) * (visibility / vws) * (visible / vws); }
-                if (ows > 0.0f) flags |= 4;
-            }
-        }
-        float consistency = 0.0f;
-        int view_counter = 0;
-        for (int n = 0; n < ns; ++n) {   // clcode.cl:1614-1622, views in subset order
-            const float tn = __shfl_sync(FULL, term, obase + n);
-            const int fn = __shfl_sync(FULL, flags, obase + n);
-            if (fn & 1) {
-                view_counter++;
-                if (fn & 2) consistency += tn;
-                if (fn & 4) consistency = (float)((double)consistency + half_fly);
-            }
-        }
-        if (act) {
-            const float margin = (float)0.01;
-            const float cs1 = view_counter > 0 ? fmaxf(margin, consistency / (float)view_counter) : margin;
-            float smoothness = 0.0f;
-            int t = 0;
-            for (; t + 4 <= T; t += 4) {
-                const float4 p4 = *reinterpret_cast<const float4 *>(prod + t);
-                smoothness += p4.x; smoothness += p4.y; smoothness += p4.z; smoothness += p4.w;
-            }
-            for (; t < T; ++t) smoothness += prod[t];
-            const float sm1 = weight_norm > 0.0f ? smoothness / weight_norm : (float)0.000001;
-            if (l8 == 0) {
-                sh->memo_plane[nmemo % PR_MEMO] = make_float4(cd, cnx, cny, cnz);
-                sh->memo_cost[nmemo % PR_MEMO] = make_float2(sm1, cs1);
-            }
-            nmemo++;
-            accept(a.iter, pair, sm1, cs1, wsim, cd, cnx, cny, cnz, pd, pnx, pny, pnz, psm, pcs);
-        }
-        __syncwarp();   // staged terms consumed, memo visible to the octet
     }
 
     if (live && l8 == 0) {
@@ -374,7 +451,6 @@ __global__ void __launch_bounds__(PR_WARPS * 32) k_propagate(PArgs a)
         a.cost_out[zM + sp] = make_float2(psm, pcs);
     }
 }
-
 
 int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, int z0, int z1, cudaStream_t st)
 {
@@ -388,11 +464,41 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     a.K = r.no_kernel_steps < 0 ? 0 : r.no_kernel_steps;
     a.kernel_step_size = r.kernel_step_size; a.iter = r.iter; a.z0 = z0;
     a.tmax = 8 + 4 * a.K;
-    size_t smem = PR_SPB * sp_shared_bytes(a.tmax);
-    if (smem > 227 * 1024 || (double)f.V * f.N >= 2147483648.0) return -1;   // kernel_step too large for the staged term table
-    if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // candidate slots a superpixel can fill: 8 neighbours, the far neighbours whose offset fits the map
+    // (same float -> int conversion as the kernel: truncation, saturating), 8 pairs
+    long long stride = (long long)r.kernel_step_size;
+    if (r.kernel_step_size != r.kernel_step_size) stride = 0;
+    if (r.kernel_step_size >= 2147483647.0f) stride = 2147483647LL;
+    if (r.kernel_step_size <= -2147483648.0f) stride = -2147483648LL;
+    int nc = 16;
+    if (stride < (long long)(f.mw > f.mh ? f.mw : f.mh))
+        for (int i = 1; i <= a.K; ++i) {
+            long long off = (long long)i * stride;
+            if (off != (long long)(int)off) { nc += 4; continue; }   // int overflow in the kernel: be generous
+            if (off < f.mh - 1) nc += 2;
+            if (off < f.mw - 1) nc += 2;
+        }
+    a.ncmax = nc;
+    if (a.ncmax > 255) return -1;   // slot numbers are kept in bytes
+    const SpLayout L = sp_layout(a.tmax, a.ncmax);
+    size_t smem = (size_t)PR_SPB * L.total;
+    if (smem > 227 * 1024 || (double)f.V * f.N >= 2147483648.0) return -1;
+    // every neighbour at most one camera apart?  (host copy of the lists lives with the frame)
+    bool unit = f.unit_baseline != 0;
     dim3 g((f.mw + PR_OCT - 1) / PR_OCT, (f.mh + PR_WARPS - 1) / PR_WARPS, z1 - z0);
-    k_propagate<<<g, PR_WARPS * 32, smem, st>>>(a);
+    static int variant = -1;
+    if (variant < 0) { const char *e = getenv("MVS_PROP_MINB"); variant = e ? atoi(e) : 5; }
+#define PR_LAUNCH(U, B)                                                                                          \
+    do {                                                                                                         \
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        k_propagate<U, B><<<g, PR_WARPS * 32, smem, st>>>(a);                                                    \
+    } while (0)
+    if (!unit) PR_LAUNCH(false, 5);
+    else if (variant == 4) PR_LAUNCH(true, 4);
+    else if (variant == 6) PR_LAUNCH(true, 6);
+    else if (variant == 7) PR_LAUNCH(true, 7);
+    else PR_LAUNCH(true, 5);
+#undef PR_LAUNCH
     return 1;
 }
 
