@@ -24,12 +24,11 @@ __device__ __forceinline__ int d2i(double x) { return __double2int_rz(x); }
 // Horner form, scaling by two exact powers of two.
 __device__ __forceinline__ float expf_pinned(float x)
 {
-    if (x != x) return x;
-    if (x > 88.72284f) return __int_as_float(0x7f800000);
-    if (x < -104.0f) return 0.0f;
+    // branch-free: the polynomial is always evaluated and the three special ranges are selected
+    // afterwards (same values as returning early; lets the compiler interleave neighbouring calls)
     float t = fmaf(x, 1.44269504f, 12582912.0f);
     float kf = t - 12582912.0f;
-    int k = (int)kf;
+    int k = f2i(kf);
     float r = fmaf(kf, -0.693145751953125f, x);
     r = fmaf(kf, -1.428606765330187e-06f, r);
     float p = 1.9875691500e-4f;
@@ -45,6 +44,9 @@ __device__ __forceinline__ float expf_pinned(float x)
     int k2 = k - k1;
     y = y * pow2i(k1);
     y = y * pow2i(k2);
+    y = x < -104.0f ? 0.0f : y;
+    y = x > 88.72284f ? __int_as_float(0x7f800000) : y;
+    y = x != x ? x : y;
     return y;
 }
 
