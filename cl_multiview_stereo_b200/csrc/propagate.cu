@@ -96,6 +96,18 @@ __device__ __forceinline__ void near_offset(int s, int &i, int &j)
     j = t % 3 - 1;
 }
 
+// the 32-byte superpixel record {id,cx,cy,L | a,b,n,disp} as ONE 256-bit gather (LDG.E.256, sm_100):
+// one L1 request per lane instead of two
+struct Rec8 { float id, cx, cy, L, a, b, n, disp; };
+__device__ __forceinline__ Rec8 ld_rec8(const float4 *p)
+{
+    Rec8 r;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r.id), "=f"(r.cx), "=f"(r.cy), "=f"(r.L), "=f"(r.a), "=f"(r.b), "=f"(r.n), "=f"(r.disp)
+                 : "l"(p));
+    return r;
+}
+
 __device__ __forceinline__ bool same_bits(const float4 &p, const float4 &q)
 {
     return __float_as_int(p.x) == __float_as_int(q.x) && __float_as_int(p.y) == __float_as_int(q.y) &&
@@ -107,7 +119,9 @@ __device__ __forceinline__ bool same_bits(const float4 &p, const float4 &q)
 // UNIT: every neighbour view is at most one camera apart in x and y (neib_hor, neib_ver <= 1).
 // Then round(d * dv) == dv * round(d) exactly (dv in {-1, 0, 1}; holds for inf / NaN too), and
 // the two rounds of a sample are taken once per (plane, sample) instead of once per view.
-template <bool UNIT, int MINB>
+// MODE bit 0: records gathered with one 256-bit load; bit 1: the nine label gathers of a (plane, view)
+// are issued before the first record gather.
+template <bool UNIT, int MINB, int MODE>
 __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
 {
     extern __shared__ __align__(16) unsigned char pr_smem[];
@@ -270,7 +284,25 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                 float num = 0.0f, vws = 0.0f, ows = 0.0f, visibility = 0.0f, visible = 0.0f;
                 // three samples at a time: their label gathers, then their centre / plane gathers, are
                 // issued together (a sample that projects outside reads pixel 0 and is masked afterwards)
-#pragma unroll 1
+                uint32_t vq9[9];
+                if (MODE & 2) {
+#pragma unroll
+                    for (int k = 0; k < 9; ++k) {
+                        const float4 sd = sdi[u * 9 + k];
+                        const float4 sv = samp[k];
+                        int xp, yp;
+                        if (UNIT) {
+                            xp = f2i(sv.x - sd.z * vt.y);
+                            yp = f2i(sv.y - sd.w * vt.z);
+                        } else {
+                            xp = f2i(sv.x - round_haz(sd.x * vt.y));
+                            yp = f2i(sv.y - round_haz(sd.y * vt.z));
+                        }
+                        const bool in = (unsigned)xp < (unsigned)a.W && (unsigned)yp < (unsigned)a.H;
+                        vq9[k] = a.idx[nbase + (uint32_t)(in ? yp * a.W + xp : 0)];
+                    }
+                }
+#pragma unroll((MODE & 2) ? 3 : 1)
                 for (int k0 = 0; k0 < 9; k0 += 3) {
                     int pix[3];
                     float fxp[3], fyp[3], dik[3];
@@ -293,24 +325,30 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                     }
                     uint32_t vq[3];
 #pragma unroll
-                    for (int j = 0; j < 3; ++j) vq[j] = mbase + a.idx[nbase + (uint32_t)pix[j]];
-                    float4 qa[3], pl[3];
-                    float2 qb[3];
+                    for (int j = 0; j < 3; ++j) vq[j] = mbase + ((MODE & 2) ? vq9[k0 + j] : a.idx[nbase + (uint32_t)pix[j]]);
+                    float qcx[3], qcy[3], qL[3], qA[3], qB[3];
+                    float4 pl[3];
 #pragma unroll
                     for (int j = 0; j < 3; ++j) {
-                        qa[j] = a.map[2 * vq[j]];
-                        qb[j] = *reinterpret_cast<const float2 *>(a.map + 2 * vq[j] + 1);
+                        if (MODE & 1) {
+                            const Rec8 r = ld_rec8(a.map + 2 * vq[j]);
+                            qcx[j] = r.cx; qcy[j] = r.cy; qL[j] = r.L; qA[j] = r.a; qB[j] = r.b;
+                        } else {
+                            const float4 qa = a.map[2 * vq[j]];
+                            const float2 qb = *reinterpret_cast<const float2 *>(a.map + 2 * vq[j] + 1);
+                            qcx[j] = qa.y; qcy[j] = qa.z; qL[j] = qa.w; qA[j] = qb.x; qB[j] = qb.y;
+                        }
                         pl[j] = a.plane_in[vq[j]];
                     }
 #pragma unroll
                     for (int j = 0; j < 3; ++j)
                         if (inb[j]) {
-                            const float d_proj = (pl[j].y * (qa[j].y - fxp[j]) + pl[j].z * (qa[j].z - fyp[j]) + pl[j].w * pl[j].x) / pl[j].w;
+                            const float d_proj = (pl[j].y * (qcx[j] - fxp[j]) + pl[j].z * (qcy[j] - fyp[j]) + pl[j].w * pl[j].x) / pl[j].w;
                             const float diff = d_proj - dik[j];
                             // visible += when_visible * exp(..): 0 * exp is +0 unless diff is NaN
                             if (fabsf(diff) < a.fuse) { visible += expf_pinned(-diff * diff * a.alpha); vws += 1.0f; }
                             else { if (diff != diff) visible += diff; ows += 1.0f; }
-                            const float cdiff = dist3(qa[j].w, qb[j].x, qb[j].y, cL, ca, cb);
+                            const float cdiff = dist3(qL[j], qA[j], qB[j], cL, ca, cb);
                             visibility += expf_pinned(-cdiff * cdiff * a.gamma);
                             num += 1.0f;
                         }
@@ -486,18 +524,22 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     // every neighbour at most one camera apart?  (host copy of the lists lives with the frame)
     bool unit = f.unit_baseline != 0;
     dim3 g((f.mw + PR_OCT - 1) / PR_OCT, (f.mh + PR_WARPS - 1) / PR_WARPS, z1 - z0);
-    static int variant = -1;
+    static int variant = -1, mode = -1;
     if (variant < 0) { const char *e = getenv("MVS_PROP_MINB"); variant = e ? atoi(e) : 5; }
-#define PR_LAUNCH(U, B)                                                                                          \
+    if (mode < 0) { const char *e = getenv("MVS_PROP_MODE"); mode = e ? atoi(e) : 1; }
+#define PR_LAUNCH(U, B, Mo)                                                                                      \
     do {                                                                                                         \
-        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        k_propagate<U, B><<<g, PR_WARPS * 32, smem, st>>>(a);                                                    \
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B, Mo>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        k_propagate<U, B, Mo><<<g, PR_WARPS * 32, smem, st>>>(a);                                                \
     } while (0)
-    if (!unit) PR_LAUNCH(false, 5);
-    else if (variant == 4) PR_LAUNCH(true, 4);
-    else if (variant == 6) PR_LAUNCH(true, 6);
-    else if (variant == 7) PR_LAUNCH(true, 7);
-    else PR_LAUNCH(true, 5);
+    if (!unit) PR_LAUNCH(false, 5, 1);
+    else if (variant == 4 && mode == 1) PR_LAUNCH(true, 4, 1);
+    else if (variant == 6 && mode == 1) PR_LAUNCH(true, 6, 1);
+    else if (variant == 4 && mode == 3) PR_LAUNCH(true, 4, 3);
+    else if (mode == 0) PR_LAUNCH(true, 5, 0);
+    else if (mode == 2) PR_LAUNCH(true, 5, 2);
+    else if (mode == 3) PR_LAUNCH(true, 5, 3);
+    else PR_LAUNCH(true, 5, 1);
 #undef PR_LAUNCH
     return 1;
 }
