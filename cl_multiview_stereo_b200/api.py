@@ -16,6 +16,7 @@ import numpy as np
 from ._native import MvsError, Params, check, lib
 
 BUF_RGBX, BUF_LAB, BUF_IDX, BUF_MAP, BUF_REP, BUF_FLAT, BUF_STATE_A, BUF_STATE_B, BUF_DISP = range(9)
+BUF_DISP_PROJ, BUF_DISP_FUSED = 9, 10   # multi-view fusion (allocated by Frame.view_fusion)
 STAGES = ("slic", "boundary", "block_match", "flatness", "init_state", "propagate", "fusion", "exchange")
 
 
@@ -175,6 +176,7 @@ class Frame:
         BUF_RGBX: ("N", 4, np.uint8), BUF_LAB: ("N", 4, np.float32), BUF_IDX: ("N", 1, np.uint32),
         BUF_MAP: ("M", 8, np.float32), BUF_REP: ("M", 8, np.uint8), BUF_FLAT: ("M", 2, np.float32),
         BUF_STATE_A: ("M", 6, np.float32), BUF_STATE_B: ("M", 6, np.float32), BUF_DISP: ("N", 1, np.float32),
+        BUF_DISP_PROJ: ("N", 1, np.float32), BUF_DISP_FUSED: ("N", 1, np.float32),
     }
 
     def __init__(self, ctx, settings, width, height, view_lo=0, view_hi=None):
@@ -249,6 +251,11 @@ class Frame:
     def fusion(self):
         check(lib().mvs_frame_fusion(self._h))
 
+    def view_fusion(self):
+        """multi-view fusion of BUF_DISP (all views) -> BUF_DISP_PROJ, BUF_DISP_FUSED; the stage the
+        reference keeps disabled (depth_refinement.cpp:1382-1451), not part of run()"""
+        check(lib().mvs_frame_view_fusion(self._h))
+
     def refine(self):
         check(lib().mvs_frame_refine(self._h))
 
@@ -317,3 +324,15 @@ def refine_run(ctx, mp, idx, rep, S, aw, ah, bl_ratio, subset_mat, subset_num, g
                                _ptr(sm), _ptr(sn), C.c_float(gamma), C.c_float(alpha), C.c_float(fuse),
                                kernel_step, kernel_size, no_prop, _ptr(flat), _ptr(sa), _ptr(sb), _ptr(disp)))
     return flat, sa, sb, disp
+
+
+def view_fusion_run(ctx, disp, aw, bl_ratio, fuse):
+    """the disabled tail of clDepthRefinement::fusion (depth_refinement.cpp:1382-1451) on a stack of
+    per-view disparity images [V,H,W] -> (disp_proj, disp_fused).  fuse as in system_settings."""
+    disp = np.ascontiguousarray(disp, np.float32)
+    V, H, W = disp.shape
+    proj = np.empty_like(disp)
+    out = np.empty_like(disp)
+    check(lib().mvs_view_fusion_run(ctx._h, V, W, H, aw, C.c_float(bl_ratio), C.c_float(fuse), _ptr(disp), _ptr(proj),
+                                    _ptr(out)))
+    return proj, out

@@ -240,7 +240,9 @@ static size_t elem_bytes(const mvs_frame *f, int which, bool *per_pixel)
     case MVS_BUF_RGBX: *per_pixel = true; return 4;
     case MVS_BUF_LAB: *per_pixel = true; return 16;
     case MVS_BUF_IDX: *per_pixel = true; return 4;
-    case MVS_BUF_DISP: *per_pixel = true; return 4;
+    case MVS_BUF_DISP:
+    case MVS_BUF_DISP_PROJ:
+    case MVS_BUF_DISP_FUSED: *per_pixel = true; return 4;
     case MVS_BUF_MAP: *per_pixel = false; return 32;
     case MVS_BUF_REP: *per_pixel = false; return 8;
     case MVS_BUF_FLAT: *per_pixel = false; return 8;
@@ -258,6 +260,8 @@ static void *buf_ptr(mvs_frame *f, int which)
     case MVS_BUF_LAB: return f->d.lab;
     case MVS_BUF_IDX: return f->d.idx;
     case MVS_BUF_DISP: return f->d.disp;
+    case MVS_BUF_DISP_PROJ: return f->d.disp_proj;
+    case MVS_BUF_DISP_FUSED: return f->d.disp_fused;
     case MVS_BUF_MAP: return f->d.map;
     case MVS_BUF_REP: return f->d.rep;
     case MVS_BUF_FLAT: return f->d.flat;
@@ -318,7 +322,7 @@ extern "C" int mvs_frame_destroy(mvs_frame *f)
     cudaStreamSynchronize(f->ctx->stream);
     FrameDev &d = f->d;
     cudaFree(d.rgbx); cudaFree(d.lab); cudaFree(d.idx); cudaFree(d.idx_tmp); cudaFree(d.map); cudaFree(d.rep);
-    cudaFree(d.flat); cudaFree(d.disp); cudaFree(d.view_subset); cudaFree(d.subset_num); cudaFree(d.levels);
+    cudaFree(d.flat); cudaFree(d.disp); cudaFree(d.disp_proj); cudaFree(d.disp_fused); cudaFree(d.view_subset); cudaFree(d.subset_num); cudaFree(d.levels);
     for (int k = 0; k < 2; ++k) { cudaFree(d.plane[k]); cudaFree(d.cost[k]); cudaFree(d.state6[k]); }
     for (cudaEvent_t e : f->ev) cudaEventDestroy(e);
     delete f;
@@ -700,6 +704,46 @@ extern "C" int mvs_frame_fusion(mvs_frame *f)
     return check_launch("fusion");
 }
 
+// Multi-view fusion of the disparity images (clcode.cl:1995-2101; host sequence
+// depth_refinement.cpp:1382-1451, disabled in the reference -- not part of mvs_frame_run).  Every view
+// reads every other view's disparity image: on a sharded frame each rank first receives the images it
+// does not own (4 B/px per view, grouped ncclSend/ncclRecv), then votes its own views.
+extern "C" int mvs_frame_view_fusion(mvs_frame *f)
+{
+    if (!f) return fail("null frame");
+    if (!f->d.disp) return fail("frame has no disparity buffer");
+    CK(cudaSetDevice(f->ctx->device));
+    FrameDev &d = f->d;
+    const size_t bytes = sizeof(float) * (size_t)d.V * d.N;
+    if (!d.disp_proj) { CK(cudaMalloc(&d.disp_proj, bytes)); }
+    if (!d.disp_fused) { CK(cudaMalloc(&d.disp_fused, bytes)); }
+    cudaStream_t st = f->ctx->stream;
+    mvs_ctx *c = f->ctx;
+    if (c->comm && c->nranks > 1 && (f->lo != 0 || f->hi != d.V)) {
+        StageTimer t(f, ST_EXCH);
+        std::vector<int> lo(c->nranks), hi(c->nranks);
+        for (int r = 0; r < c->nranks; ++r) mvs_view_partition(d.V, c->nranks, r, &lo[r], &hi[r]);
+        const size_t per_view = sizeof(float) * (size_t)d.N;
+        NK(GroupStart());
+        for (int r = 0; r < c->nranks; ++r) {
+            if (r == c->rank) continue;
+            if (hi[c->rank] > lo[c->rank])
+                NK(Send((char *)d.disp + per_view * lo[c->rank], per_view * (hi[c->rank] - lo[c->rank]), ncclChar, r, c->comm, st));
+            if (hi[r] > lo[r]) NK(Recv((char *)d.disp + per_view * lo[r], per_view * (hi[r] - lo[r]), ncclChar, r, c->comm, st));
+        }
+        NK(GroupEnd());
+    } else if (f->lo != 0 || f->hi != d.V) {
+        return fail("view fusion reads every view: frame holds views [%d,%d) of %d and has no communicator", f->lo, f->hi, d.V);
+    }
+    StageTimer t(f, ST_FUSION);
+    CK(cudaMemsetAsync(d.disp_proj, 0, bytes, st));
+    CK(cudaMemsetAsync(d.disp_fused, 0, bytes, st));
+    int nl = launch_view_fusion(d, f->bl_ratio, f->fuse, f->lo, f->hi, st);
+    if (nl < 0) return fail("view fusion: %d views need more shared memory than one SM has", d.V);
+    f->ctx->launches += nl;
+    return check_launch("view_fusion");
+}
+
 extern "C" int mvs_frame_refine(mvs_frame *f)
 {
     if (mvs_frame_flatness(f) || mvs_frame_init_state(f)) return 1;
@@ -783,6 +827,27 @@ extern "C" int mvs_refine_run(mvs_ctx *ctx, int width, int height, int array_wid
              (state_a && mvs_frame_download_async(f, MVS_BUF_STATE_A, 0, V, state_a)) ||
              (state_b && mvs_frame_download_async(f, MVS_BUF_STATE_B, 0, V, state_b)) ||
              (disp && mvs_frame_download_async(f, MVS_BUF_DISP, 0, V, disp)) || mvs_ctx_sync(ctx);
+    mvs_frame_destroy(f);
+    return rc;
+}
+
+extern "C" int mvs_view_fusion_run(mvs_ctx *ctx, int view_count, int width, int height, int array_width, float bl_ratio,
+                                   float fuse, const float *disp, float *disp_proj, float *disp_fused)
+{
+    if (!disp) return fail("null disparity input");
+    if (array_width <= 0 || view_count <= 0) return fail("bad view geometry");
+    int ah = (view_count + array_width - 1) / array_width;
+    if (ah * array_width != view_count) return fail("view_count %d is not a multiple of array_width %d", view_count, array_width);
+    mvs_frame *f = nullptr;
+    // only the per-pixel disparity buffers matter here; S = 8 sizes the (unused) superpixel arrays
+    if (frame_alloc(ctx, width, height, 8, array_width, ah, false, false, true, false, &f)) return 1;
+    f->timing = false;
+    f->bl_ratio = bl_ratio;
+    f->fuse = (float)(0.5 * fuse);   // depth_refinement.cpp:1328
+    int V = view_count;
+    int rc = mvs_frame_upload_async(f, MVS_BUF_DISP, 0, V, disp) || mvs_frame_view_fusion(f) ||
+             (disp_proj && mvs_frame_download_async(f, MVS_BUF_DISP_PROJ, 0, V, disp_proj)) ||
+             (disp_fused && mvs_frame_download_async(f, MVS_BUF_DISP_FUSED, 0, V, disp_fused)) || mvs_ctx_sync(ctx);
     mvs_frame_destroy(f);
     return rc;
 }

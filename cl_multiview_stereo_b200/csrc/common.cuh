@@ -21,6 +21,8 @@ struct FrameDev {
     float2 *cost[2];    // [V][M]   {sm,cs}
     float *state6[2];   // [V][M][6] API layout, filled on export
     float *disp;        // [V][N]
+    float *disp_proj;   // [V][N]   multi-view fusion: chased disparity (allocated on demand)
+    float *disp_fused;  // [V][N]   multi-view fusion: voted disparity (allocated on demand)
     int *view_subset;   // [V][V]
     int *subset_num;    // [V]
     float *levels;      // [L]
@@ -54,6 +56,7 @@ int launch_flatness(const FrameDev &f, float gamma_flat, int z0, int z1, cudaStr
 int launch_init_state(const FrameDev &f, const RefineArgs &a, int z0, int z1, cudaStream_t st);
 int launch_propagate(const FrameDev &f, const RefineArgs &a, int src, int dst, int z0, int z1, cudaStream_t st);
 int launch_spixl_to_image(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);
+int launch_view_fusion(const FrameDev &f, float bl_ratio, float fuse, int z0, int z1, cudaStream_t st);
 int launch_export_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
 int launch_import_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
 

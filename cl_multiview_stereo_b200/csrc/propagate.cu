@@ -119,9 +119,7 @@ __device__ __forceinline__ bool same_bits(const float4 &p, const float4 &q)
 // UNIT: every neighbour view is at most one camera apart in x and y (neib_hor, neib_ver <= 1).
 // Then round(d * dv) == dv * round(d) exactly (dv in {-1, 0, 1}; holds for inf / NaN too), and
 // the two rounds of a sample are taken once per (plane, sample) instead of once per view.
-// MODE bit 0: records gathered with one 256-bit load; bit 1: the nine label gathers of a (plane, view)
-// are issued before the first record gather.
-template <bool UNIT, int MINB, int MODE>
+template <bool UNIT, int MINB>
 __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
 {
     extern __shared__ __align__(16) unsigned char pr_smem[];
@@ -284,25 +282,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                 float num = 0.0f, vws = 0.0f, ows = 0.0f, visibility = 0.0f, visible = 0.0f;
                 // three samples at a time: their label gathers, then their centre / plane gathers, are
                 // issued together (a sample that projects outside reads pixel 0 and is masked afterwards)
-                uint32_t vq9[9];
-                if (MODE & 2) {
-#pragma unroll
-                    for (int k = 0; k < 9; ++k) {
-                        const float4 sd = sdi[u * 9 + k];
-                        const float4 sv = samp[k];
-                        int xp, yp;
-                        if (UNIT) {
-                            xp = f2i(sv.x - sd.z * vt.y);
-                            yp = f2i(sv.y - sd.w * vt.z);
-                        } else {
-                            xp = f2i(sv.x - round_haz(sd.x * vt.y));
-                            yp = f2i(sv.y - round_haz(sd.y * vt.z));
-                        }
-                        const bool in = (unsigned)xp < (unsigned)a.W && (unsigned)yp < (unsigned)a.H;
-                        vq9[k] = a.idx[nbase + (uint32_t)(in ? yp * a.W + xp : 0)];
-                    }
-                }
-#pragma unroll((MODE & 2) ? 3 : 1)
+#pragma unroll 1
                 for (int k0 = 0; k0 < 9; k0 += 3) {
                     int pix[3];
                     float fxp[3], fyp[3], dik[3];
@@ -325,19 +305,14 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                     }
                     uint32_t vq[3];
 #pragma unroll
-                    for (int j = 0; j < 3; ++j) vq[j] = mbase + ((MODE & 2) ? vq9[k0 + j] : a.idx[nbase + (uint32_t)pix[j]]);
+                    for (int j = 0; j < 3; ++j) vq[j] = mbase + a.idx[nbase + (uint32_t)pix[j]];
                     float qcx[3], qcy[3], qL[3], qA[3], qB[3];
                     float4 pl[3];
 #pragma unroll
                     for (int j = 0; j < 3; ++j) {
-                        if (MODE & 1) {
-                            const Rec8 r = ld_rec8(a.map + 2 * vq[j]);
-                            qcx[j] = r.cx; qcy[j] = r.cy; qL[j] = r.L; qA[j] = r.a; qB[j] = r.b;
-                        } else {
-                            const float4 qa = a.map[2 * vq[j]];
-                            const float2 qb = *reinterpret_cast<const float2 *>(a.map + 2 * vq[j] + 1);
-                            qcx[j] = qa.y; qcy[j] = qa.z; qL[j] = qa.w; qA[j] = qb.x; qB[j] = qb.y;
-                        }
+                        // one 256-bit gather instead of a 128-bit + a 64-bit one: 17.8 -> 16.1 ms per frame
+                        const Rec8 r = ld_rec8(a.map + 2 * vq[j]);
+                        qcx[j] = r.cx; qcy[j] = r.cy; qL[j] = r.L; qA[j] = r.a; qB[j] = r.b;
                         pl[j] = a.plane_in[vq[j]];
                     }
 #pragma unroll
@@ -524,22 +499,13 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     // every neighbour at most one camera apart?  (host copy of the lists lives with the frame)
     bool unit = f.unit_baseline != 0;
     dim3 g((f.mw + PR_OCT - 1) / PR_OCT, (f.mh + PR_WARPS - 1) / PR_WARPS, z1 - z0);
-    static int variant = -1, mode = -1;
-    if (variant < 0) { const char *e = getenv("MVS_PROP_MINB"); variant = e ? atoi(e) : 5; }
-    if (mode < 0) { const char *e = getenv("MVS_PROP_MODE"); mode = e ? atoi(e) : 1; }
-#define PR_LAUNCH(U, B, Mo)                                                                                      \
+#define PR_LAUNCH(U, B)                                                                                          \
     do {                                                                                                         \
-        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B, Mo>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        k_propagate<U, B, Mo><<<g, PR_WARPS * 32, smem, st>>>(a);                                                \
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        k_propagate<U, B><<<g, PR_WARPS * 32, smem, st>>>(a);                                                    \
     } while (0)
-    if (!unit) PR_LAUNCH(false, 5, 1);
-    else if (variant == 4 && mode == 1) PR_LAUNCH(true, 4, 1);
-    else if (variant == 6 && mode == 1) PR_LAUNCH(true, 6, 1);
-    else if (variant == 4 && mode == 3) PR_LAUNCH(true, 4, 3);
-    else if (mode == 0) PR_LAUNCH(true, 5, 0);
-    else if (mode == 2) PR_LAUNCH(true, 5, 2);
-    else if (mode == 3) PR_LAUNCH(true, 5, 3);
-    else PR_LAUNCH(true, 5, 1);
+    if (!unit) PR_LAUNCH(false, 5);
+    else PR_LAUNCH(true, 5);
 #undef PR_LAUNCH
     return 1;
 }

@@ -146,3 +146,17 @@ void clDepthRefinement::do_refinement(float gamma, float alpha, float fuse, int 
                         (float *)flatness_map.data(), current_state.data(), current_state2.data(), disp_img.data()),
          "clDepthRefinement::do_refinement");
 }
+
+void clDepthRefinement::multi_view_fusion(float fuse)
+{
+    size_t N = (size_t)img_size.x * img_size.y * view_count;
+    if (disp_img.size() != N) {
+        printText("ERROR: multi_view_fusion called before do_refinement");
+        throw std::runtime_error("clDepthRefinement::multi_view_fusion: no disparity images");
+    }
+    disp_proj.resize(N);
+    disp_fused.resize(N);
+    must(mvs_view_fusion_run(need_ctx(program, "clDepthRefinement"), view_count, img_size.x, img_size.y, array_width,
+                             bl_ratio, fuse, disp_img.data(), disp_proj.data(), disp_fused.data()),
+         "clDepthRefinement::multi_view_fusion");
+}

@@ -26,6 +26,13 @@ public:
     const float *state_b() const { return current_state2.data(); }
     const float *disparity() const { return disp_img.data(); }       /* [V][H][W] */
 
+    /* additive: the multi-view fusion the reference keeps commented out at the end of fusion()
+     * (depth_refinement.cpp:1382-1451: project_to_reference_inv + remove_view_inconsistency per
+     * reference view).  Call after do_refinement; fuse as given to do_refinement. */
+    void multi_view_fusion(float fuse);
+    const float *disparity_projected() const { return disp_proj.data(); }   /* [V][H][W] */
+    const float *disparity_fused() const { return disp_fused.data(); }      /* [V][H][W] */
+
 private:
     cl::Program program;
     vec2i img_size;
@@ -37,7 +44,7 @@ private:
     std::vector<int> subset_num;
     std::vector<int> view_subset;     /* [V][V], row stride V (depth_refinement.cpp:25-31) */
     std::vector<vec2f> flatness_map;
-    std::vector<float> current_state, current_state2, disp_img;
+    std::vector<float> current_state, current_state2, disp_img, disp_proj, disp_fused;
     vec8f *spixl_map;
     cl_uint *idx_img;
     vec8u *spixl_rep;

@@ -57,7 +57,8 @@ typedef struct mvs_params {
 /* selectors for mvs_frame_download / mvs_frame_upload / mvs_frame_dev_ptr */
 enum mvs_buffer {
     MVS_BUF_RGBX = 0, MVS_BUF_LAB = 1, MVS_BUF_IDX = 2, MVS_BUF_MAP = 3, MVS_BUF_REP = 4,
-    MVS_BUF_FLAT = 5, MVS_BUF_STATE_A = 6, MVS_BUF_STATE_B = 7, MVS_BUF_DISP = 8
+    MVS_BUF_FLAT = 5, MVS_BUF_STATE_A = 6, MVS_BUF_STATE_B = 7, MVS_BUF_DISP = 8,
+    MVS_BUF_DISP_PROJ = 9, MVS_BUF_DISP_FUSED = 10   /* multi-view fusion, allocated by mvs_frame_view_fusion */
 };
 
 const char *mvs_last_error(void);
@@ -117,6 +118,11 @@ int mvs_frame_flatness(mvs_frame *f);
 int mvs_frame_init_state(mvs_frame *f);
 int mvs_frame_propagate(mvs_frame *f, int iter);
 int mvs_frame_fusion(mvs_frame *f);
+/* multi-view fusion: project_to_reference_inv + remove_view_inconsistency per reference view
+ * (clcode.cl:1995-2101) in the host sequence the reference keeps disabled (depth_refinement.cpp:1382-1451),
+ * disp_proj zero-filled.  Reads MVS_BUF_DISP of ALL views, fills MVS_BUF_DISP_PROJ and MVS_BUF_DISP_FUSED.
+ * Not part of mvs_frame_run (the shipped pipeline stops at spixl_to_image). */
+int mvs_frame_view_fusion(mvs_frame *f);
 /* pipeline::exe_pipeline with perform_depth_est enabled (pipeline.cpp:60-64, 108-151) */
 int mvs_frame_run(mvs_frame *f);
 /* multi-GPU halo exchange of the buffers neighbouring views read (no-op without a communicator) */
@@ -149,6 +155,12 @@ int mvs_refine_run(mvs_ctx *ctx, int width, int height, int array_width, int arr
                    const int *view_subset, const int *subset_num, float gamma, float alpha, float fuse,
                    int kernel_step, int kernel_size, int no_prop, float *flat, float *state_a, float *state_b,
                    float *disp);
+
+/* the disabled tail of clDepthRefinement::fusion (depth_refinement.cpp:1382-1451) on host arrays:
+ * disp float[V*N] in; disp_proj / disp_fused float[V*N] out (either may be NULL).  fuse is
+ * system_settings::fuse (halved internally, depth_refinement.cpp:1328). */
+int mvs_view_fusion_run(mvs_ctx *ctx, int view_count, int width, int height, int array_width, float bl_ratio,
+                        float fuse, const float *disp, float *disp_proj, float *disp_fused);
 
 #ifdef __cplusplus
 }

@@ -865,6 +865,93 @@ void orc_refine(const float *map, const uint32_t *idx, const uint8_t *rep, const
 }
 
 /* ------------------------------------------------------------------------ */
+/* Multi-view fusion: kernels project_to_reference_inv (clcode.cl:1995-2034) */
+/* and remove_view_inconsistency (clcode.cl:2037-2101) in the host sequence   */
+/* the reference keeps commented out (depth_refinement.cpp:1382-1451): for    */
+/* every reference view r in turn, slice r of disp_proj is written and then   */
+/* slice r of the output is voted from ALL slices of disp_proj.  The          */
+/* reference never initialises disp_proj; the semantics pinned here are a     */
+/* zero-filled buffer (0 = "no value", clcode.cl:2056,2062), so view r sees   */
+/* the slices 0..r.  fuse is the kernel argument (host passes 0.5 * fuse_,    */
+/* depth_refinement.cpp:1328).                                                */
+/* ------------------------------------------------------------------------ */
+void orc_project_to_reference_inv(const float *full, float *proj, int ref, int V, int W, int H, int array_width,
+                                  float bl_ratio)
+{
+    size_t N = (size_t)W * H;
+    int rx = ref % array_width, ry = ref / array_width;
+#pragma omp parallel for schedule(static)
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            size_t tid = N * ref + (size_t)W * y + x;
+            float min_disp = full[tid];
+            for (int i = 0; i < V; ++i) {
+                if (i == ref) continue;
+                int cx = i % array_width, cy = i / array_width;
+                int px = o_f2i((float)x - o_roundf(min_disp * (float)(rx - cx)));
+                int py = o_f2i((float)y - o_roundf(bl_ratio * min_disp * (float)(ry - cy)));
+                if (px >= 0 && py >= 0 && px < W && py < H) {
+                    float cur = full[N * i + (size_t)W * py + px];
+                    if (min_disp < cur) min_disp = cur;
+                }
+            }
+            proj[tid] = min_disp;
+        }
+}
+
+void orc_remove_view_inconsistency(const float *proj, const float *full, float *out, int ref, int V, int W, int H,
+                                   int array_width, float bl_ratio, float fuse)
+{
+    size_t N = (size_t)W * H;
+    int rx = ref % array_width, ry = ref / array_width;
+#pragma omp parallel for schedule(static)
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            size_t pix = (size_t)W * y + x;
+            float d_est = 0.0f;
+            for (int i = 0; i < V; ++i) {
+                float d = proj[N * i + pix];
+                if (d != 0) {
+                    float stability = 0.0f;
+                    for (int j = 0; j < V; ++j) {
+                        float dc = proj[N * j + pix];
+                        if (dc != 0) {
+                            float diff = dc - d;
+                            if (fabsf(diff) > fuse) stability -= 1;
+                            if (fabsf(diff) <= fuse) stability += 1;
+                        }
+                    }
+                    for (int j = 0; j < V; ++j) {
+                        int cx = j % array_width, cy = j / array_width;
+                        int px = o_f2i((float)x - o_roundf(d * (float)(cx - rx)));
+                        int py = o_f2i((float)y - o_roundf(bl_ratio * d * (float)(cy - ry)));
+                        if (px >= 0 && py >= 0 && px < W && py < H) {
+                            float dc = full[N * j + (size_t)W * py + px];
+                            float diff = dc - d;
+                            if (fabsf(diff) > fuse) stability -= 1;
+                            if (fabsf(diff) < fuse) stability += 1;
+                        }
+                    }
+                    if (stability >= 0 && (d_est == 0 || d_est < d)) d_est = d;
+                }
+            }
+            out[N * ref + pix] = d_est;
+        }
+}
+
+/* the whole sequence; proj and out are float[N*V], proj is zero-filled here */
+void orc_view_fusion(const float *full, float *proj, float *out, int V, int W, int H, int array_width, float bl_ratio,
+                     float fuse_)
+{
+    float fuse = (float)(0.5 * (double)fuse_);   /* depth_refinement.cpp:1328: float fuse = 0.5 * fuse_ */
+    memset(proj, 0, sizeof(float) * (size_t)W * H * V);
+    for (int r = 0; r < V; ++r) {
+        orc_project_to_reference_inv(full, proj, r, V, W, H, array_width, bl_ratio);
+        orc_remove_view_inconsistency(proj, full, out, r, V, W, H, array_width, bl_ratio, fuse);
+    }
+}
+
+/* ------------------------------------------------------------------------ */
 /* vector wrappers of the pinned math (tests compare them with libm and with
  * the CUDA copy in csrc/mvs_math.cuh)                                       */
 /* ------------------------------------------------------------------------ */

@@ -212,4 +212,25 @@ void clref_spixl_to_image(const void *map, const void *idx, const float *state, 
     });
 }
 
+// multi-view fusion exactly as the host code the reference keeps commented out would run it
+// (depth_refinement.cpp:1382-1451): per reference view, project_to_reference_inv then
+// remove_view_inconsistency, 2-D NDRanges; disp_proj zero-filled first (the reference never
+// initialises it; 0 is the kernels' own "no value").  view_num / view_neighbor arguments are unused
+// by the kernel (clcode.cl:2037-2038).
+void clref_view_fusion(const float *full, float *proj, float *out, int V, int W, int H, int array_width, float bl_ratio,
+                       float fuse_)
+{
+    int2 isz(W, H);
+    float fuse = 0.5 * fuse_;   // depth_refinement.cpp:1328
+    memset(proj, 0, sizeof(float) * (size_t)W * H * V);
+    for (int r = 0; r < V; ++r) {
+        ndrange(round_up16(W), round_up16(H), 1, [&] {
+            project_to_reference_inv((float *)full, proj, r, isz, bl_ratio, array_width, V);
+        });
+        ndrange(round_up16(W), round_up16(H), 1, [&] {
+            remove_view_inconsistency(proj, (float *)full, nullptr, nullptr, r, bl_ratio, fuse, isz, array_width, V, out);
+        });
+    }
+}
+
 } // extern "C"

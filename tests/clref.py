@@ -128,3 +128,11 @@ class ClRef:
         disp = np.zeros((V, H, W), f32)
         self.lib.clref_spixl_to_image(_p(mp), _p(idx), _p(st), _p(disp), V, W, H, mw, mh)
         return disp
+
+    def view_fusion(self, disp, aw, bl_ratio, fuse_):
+        disp = np.ascontiguousarray(disp, f32)
+        V, H, W = disp.shape
+        proj = np.zeros_like(disp)
+        out = np.zeros_like(disp)
+        self.lib.clref_view_fusion(_p(disp), _p(proj), _p(out), V, W, H, aw, _cf(bl_ratio), _cf(fuse_))
+        return proj, out

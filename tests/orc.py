@@ -184,6 +184,16 @@ class Oracle:
         self.lib.orc_spixl_to_image(_p(mp), _p(idx), _p(st), _p(disp), V, W, H, mw, mh)
         return disp
 
+    def view_fusion(self, disp, aw, bl_ratio, fuse_):
+        """multi-view fusion (project_to_reference_inv + remove_view_inconsistency per reference view);
+        returns (disp_proj, fused)"""
+        disp = np.ascontiguousarray(disp, f32)
+        V, H, W = disp.shape
+        proj = np.zeros_like(disp)
+        out = np.zeros_like(disp)
+        self.lib.orc_view_fusion(_p(disp), _p(proj), _p(out), V, W, H, aw, _cf(bl_ratio), _cf(fuse_))
+        return proj, out
+
     # ---- whole pipeline (pipeline::exe_pipeline with perform_depth_est enabled)
     def pipeline(self, rgbx, s):
         """rgbx [V,H,W,4]; s = SystemSettings-like.  Returns dict of every stage output."""

@@ -116,3 +116,28 @@ def test_golden_set_is_present():
     names = {os.path.basename(p) for p in glob.glob(os.path.join(GOLDEN, "*.npz"))}
     assert {"synth_3x2.npz", "bar_5x3_crop.npz", "slic_dance_s8_conn.npz", "slic_horse_s16.npz",
             "slic_horse_s8.npz"} <= names
+
+
+def _fusion_input(seed, aw, ah, W, H, bl):
+    """per-view disparity images of a synthetic scene: ground truth + blocky errors + holes (exact 0)"""
+    rgbx, gt = synth.make_frame(seed, W, H, aw, ah, bl_ratio=bl, n_patches=5, dmin=2, dmax=9)
+    rng = np.random.default_rng(seed)
+    d = gt.astype(np.float32)
+    noise = rng.normal(0, 0.4, size=d.shape).astype(np.float32)
+    d = d + noise
+    wrong = rng.random(d.shape) < 0.05
+    d[wrong] = rng.uniform(0, 12, size=int(wrong.sum())).astype(np.float32)
+    d[rng.random(d.shape) < 0.02] = 0.0
+    return np.ascontiguousarray(d, np.float32)
+
+
+@pytest.mark.parametrize("aw,ah,W,H,bl,fuse", [(3, 2, 64, 48, 1.0, 1.0), (2, 2, 45, 37, 0.625, 2.0), (5, 3, 48, 32, 1.0359, 1.0),
+                                               (1, 1, 20, 17, 1.0, 1.0)])
+def test_view_fusion_restatement_equals_reference_source(oracle, ref, aw, ah, W, H, bl, fuse):
+    d = _fusion_input(aw * 100 + W, aw, ah, W, H, bl)
+    proj_r, out_r = ref.view_fusion(d, aw, bl, fuse)
+    proj_o, out_o = oracle.view_fusion(d, aw, bl, fuse)
+    assert_same(proj_o, proj_r, "disp_proj")
+    assert_same(out_o, out_r, "fused disparity")
+    # what the stage is for: a fused value is 0 or one of the candidates at that pixel
+    assert ((out_o == 0) | (out_o[:, None] == proj_o[None]).any(1)).all()

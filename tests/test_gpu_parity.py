@@ -278,3 +278,36 @@ def test_cpp_host_classes_match_oracle(oracle, small_frame, tmp_path, staged):
     assert_bits_equal(mp, ref["map"], "spixl_map")
     assert_bits_equal(sa, ref["state_a"], "state A")
     assert_bits_equal(disp, ref["disp"], "disparity")
+
+
+# ---- multi-view fusion (clcode.cl:1995-2101; disabled host sequence depth_refinement.cpp:1382-1451) ----
+@pytest.mark.parametrize("aw,ah,W,H,bl,fuse", [(3, 2, 96, 64, 1.0, 1.0), (2, 2, 77, 53, 0.625, 2.0), (5, 3, 160, 96, 1.0359, 1.0),
+                                               (1, 1, 33, 20, 1.0, 1.0), (5, 5, 64, 48, 1.0, 1.0)])
+def test_view_fusion_matches_oracle(ctx, oracle, aw, ah, W, H, bl, fuse):
+    from tests.test_cpu_reference_pin import _fusion_input
+    d = _fusion_input(aw * 100 + W, aw, ah, W, H, bl)
+    proj_o, out_o = oracle.view_fusion(d, aw, bl, fuse)
+    proj, out = mvs.view_fusion_run(ctx, d, aw, bl, fuse)
+    assert_bits_equal(proj, proj_o, "disp_proj")
+    assert_bits_equal(out, out_o, "fused disparity")
+
+
+def test_view_fusion_on_pipeline_output(ctx, oracle, small_frame):
+    s, rgbx, gt, ref = small_frame
+    f = mvs.Frame(ctx, s, 192, 128)
+    try:
+        f.upload(mvs.BUF_RGBX, rgbx)
+        f.run()
+        f.view_fusion()
+        disp = f.download(mvs.BUF_DISP)
+        proj_o, out_o = oracle.view_fusion(disp, s.array_width, s.bl_ratio, s.fuse)
+        fin = np.isfinite(disp).all()
+        if fin:   # NaN disparities reproject through the pinned float->int conversion only in oracle.c and CUDA
+            assert_bits_equal(f.download(mvs.BUF_DISP_PROJ), proj_o, "disp_proj")
+            assert_bits_equal(f.download(mvs.BUF_DISP_FUSED), out_o, "fused disparity")
+        # fusing twice gives the same result (buffers are re-zeroed)
+        a = f.download(mvs.BUF_DISP_FUSED)
+        f.view_fusion()
+        assert np.array_equal(a.view(np.uint32), f.download(mvs.BUF_DISP_FUSED).view(np.uint32))
+    finally:
+        f.close()
