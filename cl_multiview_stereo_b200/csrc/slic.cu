@@ -124,6 +124,45 @@ k_assoc(const float4 *__restrict__ lab, const float4 *__restrict__ map, uint32_t
     uint32_t out[AS_PX];
     int cluster_y = row / S;
     int deltaY = (row + S / 2) / S - cluster_y;
+    if (S_T > 0 && S_T % (2 * AS_PX) == 0) {
+        // the AS_PX pixels of a thread lie in one half-cell (colb is a multiple of AS_PX, S/2 too): they share
+        // the four candidate cells, which are read from shared memory once and kept in registers
+        const int cluster_x = colb / S;
+        const int deltaX = (colb + S / 2) / S - cluster_x;
+        float cc[4][5], dy2[4];
+        int cid[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = (k >> 1) - 1, j = (k & 1) - 1;   // i outer, j inner (clcode.cl:475-479)
+            const int cix = cluster_x + j + deltaY, ciy = cluster_y + i + deltaX;
+            const bool ok = cix >= 0 && ciy >= 0 && cix < mw && ciy < mh;
+            cid[k] = ok ? ciy * mw + cix : -1;
+            const float *c = s_ctr + 5 * (ok ? (ciy - ccy0) * ncx + (cix - ccx0) : 0);
+#pragma unroll
+            for (int q = 0; q < 5; ++q) cc[k][q] = c[q];
+            const float dy = (float)row - cc[k][1];
+            dy2[k] = dy * dy;
+        }
+        float4 px[AS_PX];
+#pragma unroll
+        for (int p = 0; p < AS_PX; ++p) px[p] = colb + p < W ? vlab[colb + p] : make_float4(0, 0, 0, 0);
+#pragma unroll
+        for (int p = 0; p < AS_PX; ++p) {
+            const float fcol = (float)(colb + p);
+            float min_dist = 999999.9999f;
+            int min_id = -1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float dL = px[p].x - cc[k][2], da = px[p].y - cc[k][3], db = px[p].z - cc[k][4];
+                const float color_distance = dL * dL + da * da + db * db;
+                const float dx = fcol - cc[k][0];
+                const float space_distance = dx * dx + dy2[k];
+                const float dist = sqrtf((color_distance * max_color_dist) + weight * (space_distance * max_xy_dist));
+                if (cid[k] >= 0 && dist < min_dist) { min_dist = dist; min_id = cid[k]; }
+            }
+            out[p] = (uint32_t)min_id;
+        }
+    } else {
 #pragma unroll
     for (int p = 0; p < AS_PX; ++p) {
         int col = colb + p;
@@ -151,6 +190,7 @@ k_assoc(const float4 *__restrict__ lab, const float4 *__restrict__ map, uint32_t
                 }
             }
         out[p] = (uint32_t)min_id;   // -1 -> 0xFFFFFFFF (only when no candidate cell exists)
+    }
     }
     uint32_t *o = idx + (size_t)z * N + (size_t)row * W + colb;
     if (colb + AS_PX <= W && ((W & 3) == 0)) {
@@ -270,11 +310,33 @@ __global__ void __launch_bounds__(256) k_update_centers(const float4 *__restrict
 constexpr int UPD_THREADS = 512;
 struct UpdTile { int tcx, tcy, xext, yext, rw, rh, pitch; };
 
+// tile geometry for superpixel size S (window extent actually scanned: clSLIC.cpp:22-23, 313;
+// clcode.cl:552-566); constexpr so that the S = 8 / 16 instantiations fold every index computation
+__host__ __device__ constexpr UpdTile upd_tile(int S)
+{
+    UpdTile t{};
+    const int G = (S * S * 9 + 255) / 256;   // ceil(9 S^2 / 256), exact in integers
+    const int cpl = S * 3 / 16;
+    t.xext = cpl * 16 < 3 * S ? cpl * 16 : 3 * S;
+    const int gy = ((G + cpl - 1) / cpl) * 16;
+    t.yext = gy < 3 * S ? gy : 3 * S;
+    t.tcx = 64 / S > 1 ? 64 / S : 1;
+    t.tcy = 32 / S > 1 ? 32 / S : 1;
+    t.rw = (t.tcx - 1) * S + t.xext;
+    t.rh = (t.tcy - 1) * S + t.yext;
+    t.pitch = t.rw + ((16 - t.rw % 32) % 32 + 32) % 32;   // rows two apart in a half-warp pair land on disjoint banks
+    return t;
+}
+
+template <int S_T>
 __global__ void __launch_bounds__(UPD_THREADS) k_update_centers_tiled(const float4 *__restrict__ lab,
                                                               const uint32_t *__restrict__ idx,
                                                               float4 *__restrict__ map, int W, int H, int mw, int mh,
-                                                              int S, int N, int M, int G, int cpl, int z0, UpdTile t)
+                                                              int S_rt, int N, int M, int z0)
 {
+    const int S = S_T > 0 ? S_T : S_rt;
+    const UpdTile t = upd_tile(S);
+    const int G = (S * S * 9 + 255) / 256, cpl = S * 3 / 16;
     extern __shared__ __align__(16) unsigned char upd_smem[];
     float4 *s_lab = reinterpret_cast<float4 *>(upd_smem);
     uint32_t *s_idx = reinterpret_cast<uint32_t *>(s_lab + (size_t)t.rh * t.pitch);
@@ -317,26 +379,36 @@ __global__ void __launch_bounds__(UPD_THREADS) k_update_centers_tiled(const floa
         if (gx >= mw || gy >= mh) continue;   // warp-uniform
         const int c = gy * mw + gx;
         float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
-        int sx = 0, sy = 0, sn = 0;
+        // position and count sums are exact integers: per lane over all window tiles, one warp
+        // reduction at the end.  Per slot the lane adds 1 | k << 8 | nbr_y << 16 (count, row pair, tile row).
+        int tx = 0, ty = 0, tn = 0;
+#pragma unroll 1
         for (int g = 0; g < G; ++g) {
             const int nbr_x = g % cpl, nbr_y = g / cpl;
             if (nbr_y * 16 >= S * 3) break;
             const int pxo = nbr_x * 16 + lx;
             const bool colok = pxo < S * 3;
             float v0[8], v1[8], v2[8];
-            int tx = 0, ty = 0, tn = 0;
+            int acc = 0;
+            const int sbase = (lcy * S + nbr_y * 16 + lyh) * t.pitch + lcx * S + pxo;
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const int pyo = nbr_y * 16 + 2 * k + lyh;
                 v0[k] = 0.0f; v1[k] = 0.0f; v2[k] = 0.0f;
                 if (colok && pyo < S * 3) {
-                    const int si = (lcy * S + pyo) * t.pitch + lcx * S + pxo;
+                    const int si = sbase + 2 * k * t.pitch;
                     if (s_idx[si] == (uint32_t)c) {
                         const float4 p = s_lab[si];
                         v0[k] = p.x; v1[k] = p.y; v2[k] = p.z;
-                        tx += x0 + lcx * S + pxo; ty += y0 + lcy * S + pyo; tn += 1;
+                        acc += 1 + (k << 8);
                     }
                 }
+            }
+            {
+                const int n = acc & 255, ks = acc >> 8;
+                tn += n;
+                tx += n * (x0 + lcx * S + pxo);
+                ty += n * (y0 + lcy * S + nbr_y * 16 + lyh) + 2 * ks;
             }
 #pragma unroll
             for (int h = 4; h >= 1; h >>= 1)
@@ -349,11 +421,11 @@ __global__ void __launch_bounds__(UPD_THREADS) k_update_centers_tiled(const floa
                 a1 += __shfl_down_sync(0xffffffffu, a1, o);
                 a2 += __shfl_down_sync(0xffffffffu, a2, o);
             }
-            sx += __reduce_add_sync(0xffffffffu, tx);
-            sy += __reduce_add_sync(0xffffffffu, ty);
-            sn += __reduce_add_sync(0xffffffffu, tn);
             c0 = c0 + a0; c1 = c1 + a1; c2 = c2 + a2;
         }
+        const int sx = __reduce_add_sync(0xffffffffu, tx);
+        const int sy = __reduce_add_sync(0xffffffffu, ty);
+        const int sn = __reduce_add_sync(0xffffffffu, tn);
         if (lane == 0) {
             float4 *m = map + 2 * ((size_t)z * M + c);
             const float keep7 = m[1].w;
@@ -373,26 +445,21 @@ int launch_update_centers(const FrameDev &f, int z0, int z1, cudaStream_t st)
 {
     if (z1 <= z0) return 0;
     const int S = f.S;
-    int G = (int)ceilf((float)(S * S * 9) / 256.0f);
+    int G = (int)ceilf((float)(S * S * 9) / 256.0f);   // clSLIC.cpp:22-23
     int cpl = S * 3 / 16;
-    // window extent actually scanned (clSLIC.cpp:22-23, 313; clcode.cl:552-566)
-    UpdTile t;
-    t.xext = std::min(cpl * 16, 3 * S);
-    t.yext = std::min(((G + cpl - 1) / cpl) * 16, 3 * S);
-    t.tcx = std::max(1, 64 / S);
-    t.tcy = std::max(1, 32 / S);
-    t.rw = (t.tcx - 1) * S + t.xext;
-    t.rh = (t.tcy - 1) * S + t.yext;
-    t.pitch = t.rw + ((16 - t.rw % 32) % 32 + 32) % 32;   // rows two apart in a half-warp pair land on disjoint banks
+    const UpdTile t = upd_tile(S);
     size_t smem = (size_t)t.rh * t.pitch * (sizeof(float4) + sizeof(uint32_t));
-    if (smem <= 200 * 1024) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaFuncSetAttribute(k_update_centers_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-            attr_set = true;
-        }
+    if (G == (S * S * 9 + 255) / 256 && smem <= 200 * 1024) {
         dim3 g((f.mw + t.tcx - 1) / t.tcx, (f.mh + t.tcy - 1) / t.tcy, z1 - z0);
-        k_update_centers_tiled<<<g, UPD_THREADS, smem, st>>>(f.lab, f.idx, f.map, f.W, f.H, f.mw, f.mh, S, f.N, f.M, G, cpl, z0, t);
+#define UPD_LAUNCH(ST)                                                                                              \
+    do {                                                                                                            \
+        cudaFuncSetAttribute(k_update_centers_tiled<ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
+        k_update_centers_tiled<ST><<<g, UPD_THREADS, smem, st>>>(f.lab, f.idx, f.map, f.W, f.H, f.mw, f.mh, S, f.N, f.M, z0); \
+    } while (0)
+        if (S == 8) UPD_LAUNCH(8);
+        else if (S == 16) UPD_LAUNCH(16);
+        else UPD_LAUNCH(0);
+#undef UPD_LAUNCH
         return 1;
     }
     dim3 g((f.M + 7) / 8, z1 - z0);
