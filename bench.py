@@ -376,12 +376,15 @@ def run_ours(args, rank, world, local_rank):
         st = fs.stage_ms()
         # sharded result must equal the single-GPU result bit for bit on the views this rank owns
         same = True
+        fs.set_timing(False)
+        fs.view_fusion()                   # every rank takes part in the exchange of the disparity images
+        frame.set_timing(False)
+        frame.upload(mvs.BUF_RGBX, rgbx); frame.run(); frame.view_fusion()
         if hi > lo:
-            a = fs.download(mvs.BUF_DISP, lo, hi)
-            frame.set_timing(False)
-            frame.upload(mvs.BUF_RGBX, rgbx); frame.run()
-            b = frame.download(mvs.BUF_DISP, lo, hi)
-            same = bool(np.array_equal(a.view(np.uint32), b.view(np.uint32)))
+            for which in (mvs.BUF_DISP, mvs.BUF_DISP_FUSED):
+                a = fs.download(which, lo, hi)
+                b = frame.download(which, lo, hi)
+                same = same and bool(np.array_equal(a.view(np.uint32), b.view(np.uint32)))
         same = max_over_ranks(0.0 if same else 1.0) == 0.0
         view_sharded = {"value": 1e3 / vs_ms, "unit": "frames/s", "ms_per_step": vs_ms, "scaling": "strong",
                         "views_per_rank": [mvs.view_partition(V, world, r)[1] - mvs.view_partition(V, world, r)[0]
@@ -445,13 +448,108 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------
+# SLIC-only workload (BASELINE.json configs[2]): batches of 3840x2160 images, S = 8, 5 iterations
+# ---------------------------------------------------------------------------------------------
+def run_slic_batch(args, rank, world, local_rank):
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import cl_multiview_stereo_b200 as mvs
+    from cl_multiview_stereo_b200 import synth
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    W, H, B = 3840, 2160, 16
+    s = mvs.SystemSettings(array_width=B, array_height=1)      # B independent images = a B x 1 "array"
+    imgs = np.stack([synth.voronoi_image(0x5EED0000 + rank * B + k, W, H) for k in range(B)])
+    ctx = mvs.Context(local_rank)
+    frame = mvs.Frame(ctx, s, W, H)
+    frame.upload(mvs.BUF_RGBX, imgs)
+    for _ in range(args.warmup):
+        frame.slic()
+    ctx.sync(); frame.stage_ms()
+    if dist is not None:
+        dist.barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    ctx.event_record(0)
+    for _ in range(args.steps):
+        frame.slic()
+    ctx.event_record(1)
+    ctx.sync()
+    ms = max_over_ranks(ctx.event_elapsed_ms(0, 1)) / args.steps
+    launches = ctx.launches - l0
+    clocks = sampler.stop() if rank == 0 else None
+    # end to end: pinned host images in, labels + centres out, every step
+    pin_in = mvs.PinnedBuffer(imgs.shape, np.uint8)
+    pin_in.array[...] = imgs
+    mw, mh = mvs.map_size(W, H, s.spixl_size)
+    pin_idx = mvs.PinnedBuffer((B, H, W), np.uint32)
+    pin_map = mvs.PinnedBuffer((B, mh, mw, 8), np.float32)
+
+    def e2e_step():
+        frame.upload(mvs.BUF_RGBX, pin_in.array, sync=False)
+        frame.slic()
+        frame.download(mvs.BUF_IDX, out=pin_idx.array, sync=False)
+        frame.download(mvs.BUF_MAP, out=pin_map.array, sync=False)
+
+    for _ in range(2):
+        e2e_step()
+    ctx.sync()
+    ctx.event_record(2)
+    for _ in range(args.steps):
+        e2e_step()
+    ctx.event_record(3)
+    ctx.sync()
+    e2e_ms = max_over_ranks(ctx.event_elapsed_ms(2, 3)) / args.steps
+    if rank == 0:
+        peak = 6650.0
+        try:
+            peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+        except Exception:
+            pass
+        alg = stage_bytes(W, H, s.spixl_size, s.no_iter, s.no_prop)["slic"] * B
+        gbs = alg / (ms * 1e-3) / 1e9
+        print(json.dumps({
+            "metric": "SLIC images/s", "value": world * B * 1e3 / ms, "unit": "images/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "slic_4k", "image": [W, H], "batch_per_step": B, "spixl_size": s.spixl_size,
+                       "no_iter": s.no_iter, "color_weight": s.slic_color_weight,
+                       "l2": "one batch (16 x 33 MB RGBX, 16 x 133 MB Lab) exceeds the 126 MB L2"},
+            "clocks": clocks,
+            "e2e": {"value": world * B * 1e3 / e2e_ms, "unit": "images/s", "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": int(imgs.nbytes), "d2h_bytes_per_step": int(pin_idx.array.nbytes + pin_map.array.nbytes),
+                    "result_checksum": int(pin_idx.array[0, ::97, ::89].sum())},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "slic (13 launches per batch)", "bound": "hbm", "achieved": gbs, "peak": peak,
+                         "unit": "GB/s", "frac": gbs / peak, "traffic": None, "alg_bytes_per_step": alg},
+            "cpu_baseline": None}), flush=True)
+    frame.close(); ctx.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="15view_1080p", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="15view_1080p", choices=sorted(WORKLOADS) + ["slic_4k"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -461,7 +559,10 @@ def main():
         run_reference(args, rank, world)
     else:
         args.warmup = max(args.warmup, 3)
-        run_ours(args, rank, world, local_rank)
+        if args.workload == "slic_4k":
+            run_slic_batch(args, rank, world, local_rank)
+        else:
+            run_ours(args, rank, world, local_rank)
 
 
 if __name__ == "__main__":

@@ -6,6 +6,7 @@
 // launches the matcher once per view; here every view is covered by one launch.
 #include "common.cuh"
 #include "mvs_math.cuh"
+#include <algorithm>
 
 namespace mvs {
 
@@ -76,14 +77,17 @@ constexpr float BM_OUTSIDE = -1.0f;   // staged term of a sample that projects o
 __global__ void __launch_bounds__(BM_WARPS * 32, 5)
 k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const uint2 *__restrict__ rep,
               const float *__restrict__ levels, int disp_num, const int *__restrict__ view_subset,
-              const int *__restrict__ subset_num, int aw, int V, int W, int H, int N, int M, float bl_ratio, int z0)
+              const int *__restrict__ subset_num, int aw, int V, int W, int H, int N, int M, float bl_ratio, int z0,
+              int band_blocks)
 {
     __shared__ float4 s_ref[BM_WARPS][25];      // Lab of the reference samples
     __shared__ float2 s_xy[BM_WARPS][25];       // their pixel coordinates as floats (exact below 2^24)
     __shared__ float s_t[BM_WARPS][32 * 25];    // per (level, sample) cost terms of the current pair
     const unsigned FULL = 0xffffffffu;
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int sp = blockIdx.x * BM_WARPS + warp;
+    // grid = (blocks of a band of superpixel rows, views, bands): all views work on the same image band at the
+    // same time, so the neighbour views' Lab rows a band reads stay in L2 across the views that share them
+    int sp = (blockIdx.z * band_blocks + blockIdx.x) * BM_WARPS + warp;
     int z = z0 + blockIdx.y;
     if (sp >= M) return;   // whole warp leaves together
     size_t mi = (size_t)z * M + sp;
@@ -194,9 +198,13 @@ k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const ui
 int launch_block_match(const FrameDev &f, float bl_ratio, int z0, int z1, cudaStream_t st)
 {
     if (z1 <= z0) return 0;
-    dim3 g((f.M + BM_WARPS - 1) / BM_WARPS, z1 - z0);
+    const int nblocks = (f.M + BM_WARPS - 1) / BM_WARPS;
+    int band_blocks = std::max(1, (2 * f.mw + BM_WARPS - 1) / BM_WARPS);   // two superpixel rows per band
+    int bands = (nblocks + band_blocks - 1) / band_blocks;
+    if (bands > 65535) { band_blocks = (nblocks + 65534) / 65535; bands = (nblocks + band_blocks - 1) / band_blocks; }
+    dim3 g(band_blocks, z1 - z0, bands);
     k_block_match<<<g, BM_WARPS * 32, 0, st>>>(f.lab, f.map, f.rep, f.levels, f.num_levels, f.view_subset,
-                                               f.subset_num, f.aw, f.V, f.W, f.H, f.N, f.M, bl_ratio, z0);
+                                               f.subset_num, f.aw, f.V, f.W, f.H, f.N, f.M, bl_ratio, z0, band_blocks);
     return 1;
 }
 

@@ -127,7 +127,9 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int l8 = lane & 7, obase = lane & 24;
     const unsigned lower8 = (1u << l8) - 1u;
-    const int x = blockIdx.x * PR_OCT + (lane >> 3), y = blockIdx.y * PR_WARPS + warp, z = a.z0 + blockIdx.z;
+    // grid = (column tiles, views, row tiles): the views of one band of rows run together, so the label rows
+    // and records a band gathers from its neighbour views are still in L2 when those views reach the band
+    const int x = blockIdx.x * PR_OCT + (lane >> 3), y = blockIdx.z * PR_WARPS + warp, z = a.z0 + blockIdx.y;
     const bool live = x < a.mw && y < a.mh;
 
     const SpLayout L = sp_layout(a.tmax, a.ncmax);
@@ -498,7 +500,7 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     if (smem > 227 * 1024 || (double)f.V * f.N >= 2147483648.0) return -1;
     // every neighbour at most one camera apart?  (host copy of the lists lives with the frame)
     bool unit = f.unit_baseline != 0;
-    dim3 g((f.mw + PR_OCT - 1) / PR_OCT, (f.mh + PR_WARPS - 1) / PR_WARPS, z1 - z0);
+    dim3 g((f.mw + PR_OCT - 1) / PR_OCT, z1 - z0, (f.mh + PR_WARPS - 1) / PR_WARPS);
 #define PR_LAUNCH(U, B)                                                                                          \
     do {                                                                                                         \
         if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \

@@ -86,7 +86,10 @@ void pipeline::run_device_resident()
     must(mvs_frame_create(program.ctx(), &p, 0, view_num, &f), "pipeline: frame");
     disp_img.resize(N);
     state_a_.resize(6 * M);
+    if (multi_view_fusion) disp_fused_.resize(N);
     int rc = mvs_frame_upload_async(f, MVS_BUF_RGBX, 0, view_num, in_img.data()) || mvs_frame_run(f) ||
+             (multi_view_fusion && (mvs_frame_view_fusion(f) ||
+                                    mvs_frame_download_async(f, MVS_BUF_DISP_FUSED, 0, view_num, disp_fused_.data()))) ||
              mvs_frame_download_async(f, MVS_BUF_LAB, 0, view_num, cvt_img) ||
              mvs_frame_download_async(f, MVS_BUF_IDX, 0, view_num, idx_img) ||
              mvs_frame_download_async(f, MVS_BUF_MAP, 0, view_num, spixl_map) ||
@@ -152,4 +155,8 @@ void pipeline::refine_depth_map(std::vector<std::vector<int> > &view_subset)
     size_t N = (size_t)img_size.x * img_size.y * view_num, M = (size_t)map_size.x * map_size.y * view_num;
     disp_img.assign(refinement_obj.disparity(), refinement_obj.disparity() + N);
     state_a_.assign(refinement_obj.state_a(), refinement_obj.state_a() + 6 * M);
+    if (multi_view_fusion) {
+        refinement_obj.multi_view_fusion(settings->fuse);
+        disp_fused_.assign(refinement_obj.disparity_fused(), refinement_obj.disparity_fused() + N);
+    }
 }

@@ -42,7 +42,7 @@ int main(int argc, char **argv)
 
     std::string list = argc > 1 ? argv[1] : "data.txt";
     std::string out_dir;
-    bool staged = false;
+    bool staged = false, view_fusion = false;
     for (int i = 2; i < argc; ++i) {
         const char *eq = strchr(argv[i], '=');
         if (!eq) { out_dir = argv[i]; continue; }
@@ -67,12 +67,14 @@ int main(int argc, char **argv)
         else if (k == "alpha") s->alpha = (float)v;
         else if (k == "no_prop") s->no_prop = (int)v;
         else if (k == "staged") staged = v != 0;
+        else if (k == "multi_view_fusion") view_fusion = v != 0;
         else { std::cout << "unknown setting " << k << std::endl; return 2; }
     }
 
     try {
         pipeline *model = new pipeline(list, s);
         model->device_resident = !staged;
+        model->multi_view_fusion = view_fusion;
         auto t0 = std::chrono::high_resolution_clock::now();
         model->exe_pipeline();
         auto t1 = std::chrono::high_resolution_clock::now();
@@ -88,6 +90,7 @@ int main(int argc, char **argv)
             dump(out_dir + "/rep.bin", model->extents(), M * sizeof(vec8u));
             dump(out_dir + "/state_a.bin", model->state_a(), M * 6 * sizeof(float));
             dump(out_dir + "/disp.bin", model->disparity(), N * sizeof(float));
+            if (view_fusion) dump(out_dir + "/disp_fused.bin", model->disparity_fused(), N * sizeof(float));
         }
         delete model;
     } catch (const std::exception &e) {

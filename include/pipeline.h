@@ -33,6 +33,10 @@ public:
     /* additive: false = run the three stage classes one after another through host memory
      * exactly like the reference; true (default) = one device-resident frame (mvs_frame_run) */
     bool device_resident = true;
+    /* additive: also run the multi-view fusion the reference keeps disabled
+     * (depth_refinement.cpp:1382-1451); result in disparity_fused() */
+    bool multi_view_fusion = false;
+    const float *disparity_fused() const { return disp_fused_.data(); }
     /* per-stage device milliseconds of the last device-resident run (mvs_frame_stage_ms order) */
     float stage_ms[8];
 
@@ -50,5 +54,5 @@ private:
     cl_uint *idx_img;
     vec8f *spixl_map;
     vec8u *spixl_rep;
-    std::vector<float> disp_img, state_a_;
+    std::vector<float> disp_img, state_a_, disp_fused_;
 };

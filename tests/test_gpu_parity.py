@@ -264,7 +264,7 @@ def test_cpp_host_classes_match_oracle(oracle, small_frame, tmp_path, staged):
             fh.write(f"v{v}.ppm\n")
     args = [exe, str(tmp_path / "data.txt"), str(tmp_path), f"array_width={s.array_width}", f"array_height={s.array_height}",
             f"min_disp={s.min_disp}", f"max_disp={s.max_disp}", f"inc={s.inc}", f"bl_ratio={s.bl_ratio}",
-            f"kernel_size={s.kernel_size}", f"staged={staged}"]
+            f"kernel_size={s.kernel_size}", f"staged={staged}", "multi_view_fusion=1"]
     out = subprocess.run(args, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     mh, mw = ref["map"].shape[1:3]
@@ -278,6 +278,9 @@ def test_cpp_host_classes_match_oracle(oracle, small_frame, tmp_path, staged):
     assert_bits_equal(mp, ref["map"], "spixl_map")
     assert_bits_equal(sa, ref["state_a"], "state A")
     assert_bits_equal(disp, ref["disp"], "disparity")
+    fused = np.fromfile(tmp_path / "disp_fused.bin", np.float32).reshape(V, H, W)
+    if np.isfinite(ref["disp"]).all():
+        assert_bits_equal(fused, oracle.view_fusion(ref["disp"], s.array_width, s.bl_ratio, s.fuse)[1], "fused disparity")
 
 
 # ---- multi-view fusion (clcode.cl:1995-2101; disabled host sequence depth_refinement.cpp:1382-1451) ----
