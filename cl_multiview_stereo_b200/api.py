@@ -228,6 +228,21 @@ class Frame:
         check(fn(self._h, which, v0, v1, _ptr(out)))
         return out
 
+    def upload_bgr(self, bgr, v0=0, v1=None):
+        """loadImageIn on the device: packed BGR rasters [v1-v0, H, W, 3] (cv::Mat order) -> BUF_RGBX"""
+        v1 = self.V if v1 is None else v1
+        a = np.ascontiguousarray(bgr, dtype=np.uint8)
+        if a.size != (v1 - v0) * self.H * self.W * 3:
+            raise MvsError(f"upload_bgr: expected {(v1 - v0, self.H, self.W, 3)}, got {a.shape}")
+        check(lib().mvs_frame_upload_bgr(self._h, v0, v1, _ptr(a)))
+
+    def export_u8(self, which, min_disp, max_disp, element=0, v0=0, v1=None):
+        """8-bit visualisation image quantised on the device (plot_full_image / img_translate_state)"""
+        v1 = self.V if v1 is None else v1
+        out = np.empty((v1 - v0, self.H, self.W), np.uint8)
+        check(lib().mvs_frame_export_u8(self._h, which, int(element), int(min_disp), int(max_disp), v0, v1, _ptr(out)))
+        return out
+
     def dev_ptr(self, which):
         p = C.c_void_p()
         check(lib().mvs_frame_dev_ptr(self._h, which, C.byref(p)))

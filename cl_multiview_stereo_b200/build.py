@@ -35,7 +35,7 @@ def _newer(target, sources):
 
 
 def build_native(force=False, verbose=False):
-    cu = [os.path.join(CSRC, f) for f in ("slic.cu", "photo.cu", "refine.cu", "propagate.cu", "fuse.cu", "capi.cu")]
+    cu = [os.path.join(CSRC, f) for f in ("slic.cu", "photo.cu", "refine.cu", "propagate.cu", "fuse.cu", "io.cu", "capi.cu")]
     deps = cu + [os.path.join(CSRC, f) for f in ("common.cuh", "mvs_math.cuh")] + [os.path.join(ROOT, "include", "mvs_capi.h")]
     if force or _newer(LIB, deps):
         cmd = [_nvcc()] + NVCC_FLAGS + ["-shared", "-o", LIB] + cu + ["-ldl"]

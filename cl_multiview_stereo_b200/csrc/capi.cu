@@ -322,7 +322,7 @@ extern "C" int mvs_frame_destroy(mvs_frame *f)
     cudaStreamSynchronize(f->ctx->stream);
     FrameDev &d = f->d;
     cudaFree(d.rgbx); cudaFree(d.lab); cudaFree(d.idx); cudaFree(d.idx_tmp); cudaFree(d.map); cudaFree(d.rep);
-    cudaFree(d.flat); cudaFree(d.disp); cudaFree(d.disp_proj); cudaFree(d.disp_fused); cudaFree(d.view_subset); cudaFree(d.subset_num); cudaFree(d.levels);
+    cudaFree(d.flat); cudaFree(d.disp); cudaFree(d.disp_proj); cudaFree(d.disp_fused); cudaFree(d.io_stage); cudaFree(d.view_subset); cudaFree(d.subset_num); cudaFree(d.levels);
     for (int k = 0; k < 2; ++k) { cudaFree(d.plane[k]); cudaFree(d.cost[k]); cudaFree(d.state6[k]); }
     for (cudaEvent_t e : f->ev) cudaEventDestroy(e);
     delete f;
@@ -760,6 +760,59 @@ extern "C" int mvs_frame_run(mvs_frame *f)
     if (f->ctx->comm && f->ctx->nranks > 1)
         if (mvs_frame_exchange(f, MVS_BUF_MAP)) return 1;
     return mvs_frame_refine(f);
+}
+
+// ---- device-side ingest / export -------------------------------------
+static int need_io_stage(mvs_frame *f)
+{
+    if (!f->d.io_stage) CK(cudaMalloc(&f->d.io_stage, (size_t)f->d.V * f->d.N * 3));
+    return 0;
+}
+
+// loadImageIn (file_handler.cpp:6-15) for views [v0, v1): `bgr` is the packed 3-byte BGR raster of
+// those views (cv::Mat order); 3 B/px cross the bus and the repack to vec3u {R,G,B,pad} runs on the device
+extern "C" int mvs_frame_upload_bgr(mvs_frame *f, int v0, int v1, const uint8_t *bgr)
+{
+    if (!f || !bgr) return fail("null argument");
+    if (!f->d.rgbx) return fail("frame has no image buffers");
+    if (v0 < 0 || v1 > f->d.V || v0 > v1) return fail("bad view range [%d,%d)", v0, v1);
+    CK(cudaSetDevice(f->ctx->device));
+    if (need_io_stage(f)) return 1;
+    cudaStream_t st = f->ctx->stream;
+    CK(cudaMemcpyAsync(f->d.io_stage, bgr, (size_t)(v1 - v0) * f->d.N * 3, cudaMemcpyHostToDevice, st));
+    f->ctx->launches += launch_ingest_bgr(f->d, f->d.io_stage, v0, v1, st);
+    if (check_launch("ingest_bgr")) return 1;
+    CK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// 8-bit visualisation images, quantised on the device (1 B/px crosses the bus):
+//   which = MVS_BUF_DISP / MVS_BUF_DISP_FUSED: plot_full_image (depth_refinement.cpp:1476-1497)
+//   which = MVS_BUF_STATE_A / _B with element 0 (d), 1 (smoothness), 2 (consistency):
+//           img_translate_state (depth_refinement.cpp:1500-1560)
+extern "C" int mvs_frame_export_u8(mvs_frame *f, int which, int element, int min_disp, int max_disp, int v0, int v1,
+                                   uint8_t *host)
+{
+    if (!f || !host) return fail("null argument");
+    if (v0 < 0 || v1 > f->d.V || v0 > v1) return fail("bad view range [%d,%d)", v0, v1);
+    CK(cudaSetDevice(f->ctx->device));
+    if (need_io_stage(f)) return 1;
+    cudaStream_t st = f->ctx->stream;
+    const float mn = (float)min_disp, range = (float)(max_disp - min_disp);
+    if (which == MVS_BUF_DISP || which == MVS_BUF_DISP_FUSED) {
+        const float *src = (const float *)buf_ptr(f, which);
+        if (!src) return fail("buffer %d not available", which);
+        f->ctx->launches += launch_quantise_disp(f->d, src, f->d.io_stage, mn, range, v0, v1, st);
+    } else if (which == MVS_BUF_STATE_A || which == MVS_BUF_STATE_B) {
+        if (element < 0 || element > 2) return fail("state element %d: only 0 (d), 1 (smoothness), 2 (consistency)", element);
+        f->ctx->launches += launch_quantise_state(f->d, which == MVS_BUF_STATE_B, element, f->d.io_stage, mn, range, v0, v1, st);
+    } else {
+        return fail("mvs_frame_export_u8: buffer %d has no 8-bit image form", which);
+    }
+    if (check_launch("export_u8")) return 1;
+    CK(cudaMemcpyAsync(host, f->d.io_stage, (size_t)(v1 - v0) * f->d.N, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return 0;
 }
 
 // ---------------------------------------------------------------------------------------

@@ -23,6 +23,7 @@ struct FrameDev {
     float *disp;        // [V][N]
     float *disp_proj;   // [V][N]   multi-view fusion: chased disparity (allocated on demand)
     float *disp_fused;  // [V][N]   multi-view fusion: voted disparity (allocated on demand)
+    uint8_t *io_stage;  // [V][N][3] staging of packed BGR input / 8-bit output (allocated on demand)
     int *view_subset;   // [V][V]
     int *subset_num;    // [V]
     float *levels;      // [L]
@@ -57,6 +58,11 @@ int launch_init_state(const FrameDev &f, const RefineArgs &a, int z0, int z1, cu
 int launch_propagate(const FrameDev &f, const RefineArgs &a, int src, int dst, int z0, int z1, cudaStream_t st);
 int launch_spixl_to_image(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);
 int launch_view_fusion(const FrameDev &f, float bl_ratio, float fuse, int z0, int z1, cudaStream_t st);
+int launch_ingest_bgr(const FrameDev &f, const void *bgr_dev, int z0, int z1, cudaStream_t st);
+int launch_quantise_disp(const FrameDev &f, const float *src, uint8_t *out_dev, float mn, float range, int z0, int z1,
+                         cudaStream_t st);
+int launch_quantise_state(const FrameDev &f, int which, int element, uint8_t *out_dev, float mn, float range, int z0,
+                          int z1, cudaStream_t st);
 int launch_export_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
 int launch_import_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
 

@@ -1,0 +1,96 @@
+// io.cu -- device-side ingest and export of the depth pipeline (sm_100a): byte work that the
+// reference does in host loops around OpenCV.
+//   k_ingest_bgr      loadImageIn (file_handler.cpp:6-15): BGR raster (cv::Mat, 3 B/px) -> vec3u
+//                     {s0 = R, s1 = G, s2 = B, pad}; uploading 3 B/px instead of 4 and repacking here
+//   k_quantise_disp   plot_full_image (depth_refinement.cpp:1476-1497): 8-bit image of a disparity map,
+//                     (unsigned char)floor((d - min) / (max - min) * 255)
+//   k_quantise_state  img_translate_state (depth_refinement.cpp:1500-1560): per-pixel image of one state
+//                     element of the pixel's superpixel, elements 0 (d), 1 (smoothness), 2 (consistency)
+#include "common.cuh"
+#include "mvs_math.cuh"
+
+namespace mvs {
+
+// 4 pixels per thread: three 32-bit loads, one 128-bit store
+__global__ void __launch_bounds__(256) k_ingest_bgr(const uint32_t *__restrict__ bgr, uint4 *__restrict__ rgbx,
+                                                    const uint8_t *__restrict__ bgr8, uchar4 *__restrict__ rgbx1,
+                                                    size_t n, int vec)
+{
+    const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;   // quad index
+    const size_t p = 4 * q;
+    if (vec && p + 4 <= n) {
+        const uint32_t a = bgr[3 * q], b = bgr[3 * q + 1], c = bgr[3 * q + 2];   // B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
+        uint4 o;
+        o.x = ((a >> 16) & 255u) | (a & 0xff00u) | ((a & 255u) << 16);
+        o.y = ((b >> 8) & 255u) | ((b & 255u) << 8) | ((a >> 24) << 16);
+        o.z = (c & 255u) | ((b >> 24) << 8) | (((b >> 16) & 255u) << 16);
+        o.w = (c >> 24) | (((c >> 16) & 255u) << 8) | (((c >> 8) & 255u) << 16);
+        rgbx[q] = o;
+    } else {
+        for (size_t k = p; k < n && k < p + 4; ++k) rgbx1[k] = make_uchar4(bgr8[3 * k + 2], bgr8[3 * k + 1], bgr8[3 * k], 0);
+    }
+}
+
+// (unsigned char)floor(x): the reference's cast is only defined for 0 <= x < 256; outside it this pins
+// what the reference's own platform does (x86 cvttss2si then the low byte; NaN and |x| >= 2^31 give 0)
+__device__ __forceinline__ uint8_t to_u8(float x)
+{
+    const float fl = floorf(x);
+    const int v = (fl >= -2147483648.0f && fl < 2147483648.0f) ? (int)fl : (int)0x80000000;
+    return (uint8_t)(v & 255);
+}
+
+__global__ void __launch_bounds__(256) k_quantise_disp(const float *__restrict__ disp, uint8_t *__restrict__ out, size_t n,
+                                                       float mn, float range)
+{
+    const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    out[p] = to_u8(((disp[p] - mn) / range) * 255.0f);
+}
+
+__global__ void __launch_bounds__(256) k_quantise_state(const uint32_t *__restrict__ idx, const float4 *__restrict__ plane,
+                                                        const float2 *__restrict__ cost, uint8_t *__restrict__ out, int N,
+                                                        int M, int element, float mn, float range, int z0)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int z = z0 + blockIdx.y;
+    if (p >= N) return;
+    const size_t q = (size_t)z * M + idx[(size_t)z * N + p];
+    float v;
+    if (element == 0) v = ((plane[q].x - mn) / range) * 255.0f;
+    else if (element == 1) v = cost[q].x * 255.0f;
+    else v = cost[q].y * 255.0f;
+    out[(size_t)blockIdx.y * N + p] = to_u8(v);
+}
+
+int launch_ingest_bgr(const FrameDev &f, const void *bgr_dev, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    const size_t n = (size_t)(z1 - z0) * f.N;
+    const size_t quads = (n + 3) / 4;
+    uchar4 *dst = f.rgbx + (size_t)z0 * f.N;
+    k_ingest_bgr<<<(unsigned)((quads + 255) / 256), 256, 0, st>>>((const uint32_t *)bgr_dev, (uint4 *)dst,
+                                                                 (const uint8_t *)bgr_dev, dst, n,
+                                                                 ((size_t)z0 * f.N) % 4 == 0 ? 1 : 0);
+    return 1;
+}
+
+int launch_quantise_disp(const FrameDev &f, const float *src, uint8_t *out_dev, float mn, float range, int z0, int z1,
+                         cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    const size_t n = (size_t)(z1 - z0) * f.N;
+    k_quantise_disp<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src + (size_t)z0 * f.N, out_dev, n, mn, range);
+    return 1;
+}
+
+int launch_quantise_state(const FrameDev &f, int which, int element, uint8_t *out_dev, float mn, float range, int z0,
+                          int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    dim3 g((f.N + 255) / 256, z1 - z0);
+    k_quantise_state<<<g, 256, 0, st>>>(f.idx, f.plane[which], f.cost[which], out_dev, f.N, f.M, element, mn, range, z0);
+    return 1;
+}
+
+} // namespace mvs

@@ -103,6 +103,14 @@ int mvs_frame_download(mvs_frame *f, int which, int v0, int v1, void *host);
 int mvs_frame_upload_async(mvs_frame *f, int which, int v0, int v1, const void *host);
 int mvs_frame_download_async(mvs_frame *f, int which, int v0, int v1, void *host);
 int mvs_frame_dev_ptr(mvs_frame *f, int which, void **dev);
+/* loadImageIn (file_handler.cpp:6-15) on the device: packed BGR raster (cv::Mat order, 3 B/px) of views
+ * [v0,v1) -> MVS_BUF_RGBX {s0=R,s1=G,s2=B,pad} */
+int mvs_frame_upload_bgr(mvs_frame *f, int v0, int v1, const uint8_t *bgr);
+/* 8-bit visualisation images quantised on the device: plot_full_image (depth_refinement.cpp:1476-1497) for
+ * MVS_BUF_DISP / MVS_BUF_DISP_FUSED; img_translate_state (depth_refinement.cpp:1500-1560) for MVS_BUF_STATE_A/B
+ * with element 0 (d), 1 (smoothness), 2 (consistency).  host: uint8[(v1-v0)*H*W] */
+int mvs_frame_export_u8(mvs_frame *f, int which, int element, int min_disp, int max_disp, int v0, int v1,
+                        uint8_t *host);
 int mvs_frame_sizes(mvs_frame *f, int *V, int *W, int *H, int *mw, int *mh, int *num_levels);
 
 /* clSLIC::do_super_pixel_seg (clSLIC.cpp:67-122) for the frame's own views, all views per launch */

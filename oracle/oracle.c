@@ -952,6 +952,51 @@ void orc_view_fusion(const float *full, float *proj, float *out, int V, int W, i
 }
 
 /* ------------------------------------------------------------------------ */
+/* Host-side byte work of the reference (no OpenCL involved, restated from    */
+/* the C++ sources): loadImageIn (file_handler.cpp:6-15), plot_full_image     */
+/* (depth_refinement.cpp:1476-1497), img_translate_state (:1500-1560).        */
+/* The (unsigned char) cast of an out-of-range float is undefined in C; the   */
+/* value pinned is what the reference's x86 build does: cvttss2si, low byte   */
+/* (NaN and |x| >= 2^31 give 0x80000000 -> 0).                                */
+/* ------------------------------------------------------------------------ */
+void orc_load_image_in(const uint8_t *bgr, uint8_t *rgbx, int W, int H)
+{
+    for (size_t p = 0; p < (size_t)W * H; ++p) {
+        rgbx[4 * p + 0] = bgr[3 * p + 2];   /* s0 = red   */
+        rgbx[4 * p + 1] = bgr[3 * p + 1];   /* s1 = green */
+        rgbx[4 * p + 2] = bgr[3 * p + 0];   /* s2 = blue  */
+        rgbx[4 * p + 3] = 0;
+    }
+}
+
+static uint8_t o_to_u8(float x)
+{
+    float fl = floorf(x);
+    int v = (fl >= -2147483648.0f && fl < 2147483648.0f) ? (int)fl : (int)0x80000000u;
+    return (uint8_t)(v & 255);
+}
+
+void orc_plot_full_image(const float *disp, uint8_t *out, size_t n, int min_disp, int max_disp)
+{
+    for (size_t p = 0; p < n; ++p)
+        out[p] = o_to_u8(((disp[p] - (float)min_disp) / (float)(max_disp - min_disp)) * 255);
+}
+
+void orc_img_translate_state(const float *state, const uint32_t *idx, uint8_t *out, int V, int W, int H, int mw,
+                             int mh, int element, int min_disp, int max_disp)
+{
+    size_t N = (size_t)W * H, M = (size_t)mw * mh;
+    for (int k = 0; k < V; ++k)
+        for (size_t p = 0; p < N; ++p) {
+            const float *st = state + 6 * (M * k + idx[N * k + p]);
+            float v;
+            if (element == 0) v = ((st[0] - (float)min_disp) / (float)(max_disp - min_disp)) * 255;
+            else v = st[element] * 255;
+            out[N * k + p] = o_to_u8(v);
+        }
+}
+
+/* ------------------------------------------------------------------------ */
 /* vector wrappers of the pinned math (tests compare them with libm and with
  * the CUDA copy in csrc/mvs_math.cuh)                                       */
 /* ------------------------------------------------------------------------ */

@@ -194,6 +194,28 @@ class Oracle:
         self.lib.orc_view_fusion(_p(disp), _p(proj), _p(out), V, W, H, aw, _cf(bl_ratio), _cf(fuse_))
         return proj, out
 
+    # ---- host-side byte work (file_handler.cpp:6-15, depth_refinement.cpp:1476-1560)
+    def load_image_in(self, bgr):
+        bgr = np.ascontiguousarray(bgr, u8)
+        H, W, _ = bgr.shape
+        out = np.zeros((H, W, 4), u8)
+        self.lib.orc_load_image_in(_p(bgr), _p(out), W, H)
+        return out
+
+    def plot_full_image(self, disp, min_disp, max_disp):
+        disp = np.ascontiguousarray(disp, f32)
+        out = np.zeros(disp.shape, u8)
+        self.lib.orc_plot_full_image(_p(disp), _p(out), C.c_size_t(disp.size), int(min_disp), int(max_disp))
+        return out
+
+    def img_translate_state(self, state, idx, element, min_disp, max_disp):
+        V, H, W = idx.shape
+        mh, mw = state.shape[1:3]
+        out = np.zeros((V, H, W), u8)
+        self.lib.orc_img_translate_state(_p(np.ascontiguousarray(state, f32)), _p(idx), _p(out), V, W, H, mw, mh,
+                                         int(element), int(min_disp), int(max_disp))
+        return out
+
     # ---- whole pipeline (pipeline::exe_pipeline with perform_depth_est enabled)
     def pipeline(self, rgbx, s):
         """rgbx [V,H,W,4]; s = SystemSettings-like.  Returns dict of every stage output."""

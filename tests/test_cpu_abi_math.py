@@ -120,3 +120,17 @@ def test_round_and_truncation_semantics(oracle):
     oracle.lib.orc_math_f2i(x.ctypes.data_as(C.c_void_p), i.ctypes.data_as(C.c_void_p), len(x))
     assert list(i[:8]) == [0, 0, 1, 2, -2, 0, 0, 0]                          # toward zero (B5)
     assert i[8] == 2147483647 and i[9] == -2147483648 and i[10] == 0          # cvt.rzi saturation
+
+
+def test_host_byte_work_restatement(oracle):
+    """loadImageIn / plot_full_image restated in oracle.c against plain numpy (file_handler.cpp:6-15,
+    depth_refinement.cpp:1487)"""
+    rng = np.random.default_rng(5)
+    bgr = rng.integers(0, 256, size=(9, 7, 3), dtype=np.uint8)
+    out = oracle.load_image_in(bgr)
+    assert np.array_equal(out[..., :3], bgr[..., ::-1]) and (out[..., 3] == 0).all()
+    d = rng.uniform(30, 60, size=(4, 5)).astype(np.float32)
+    want = np.floor((d - np.float32(30)) / np.float32(30) * np.float32(255)).astype(np.uint8)
+    assert np.array_equal(oracle.plot_full_image(d, 30, 60), want)
+    hostile = np.array([np.nan, np.inf, -np.inf, 1e20, -1.0, 61.0], np.float32)
+    assert list(oracle.plot_full_image(hostile, 30, 60)) == [0, 0, 0, 0, (-264) & 255, 263 & 255]

@@ -314,3 +314,44 @@ def test_view_fusion_on_pipeline_output(ctx, oracle, small_frame):
         assert np.array_equal(a.view(np.uint32), f.download(mvs.BUF_DISP_FUSED).view(np.uint32))
     finally:
         f.close()
+
+
+# ---- device-side ingest / export (file_handler.cpp:6-15, depth_refinement.cpp:1476-1560) ----
+@pytest.mark.parametrize("W,H", [(192, 128), (37, 29), (141, 94)])
+def test_ingest_bgr_matches_load_image_in(ctx, oracle, W, H):
+    s = small_settings(3, 2)
+    rng = np.random.default_rng(W)
+    bgr = rng.integers(0, 256, size=(6, H, W, 3), dtype=np.uint8)
+    f = mvs.Frame(ctx, s, W, H)
+    try:
+        f.upload_bgr(bgr)
+        want = np.stack([oracle.load_image_in(bgr[v]) for v in range(6)])
+        assert np.array_equal(f.download(mvs.BUF_RGBX), want)
+        f.upload_bgr(bgr[::-1][1:3], 1, 3)      # a sub-range of views (odd pixel counts: unaligned start)
+        want[1:3] = want[::-1][1:3]
+        assert np.array_equal(f.download(mvs.BUF_RGBX), want)
+    finally:
+        f.close()
+
+
+def test_export_u8_matches_reference_quantisation(ctx, oracle, small_frame):
+    s, rgbx, gt, ref = small_frame
+    f = mvs.Frame(ctx, s, 192, 128)
+    try:
+        f.upload(mvs.BUF_RGBX, rgbx)
+        f.run()
+        disp = f.download(mvs.BUF_DISP)
+        # a few hostile values in the disparity image: the pinned out-of-range / NaN behaviour
+        disp[0, 0, :8] = [np.nan, np.inf, -np.inf, 1e20, -1e20, -3.5, 300.0, 15.999]
+        f.upload(mvs.BUF_DISP, disp)
+        for lo, hi in ((s.min_disp, s.max_disp), (3, 11)):
+            assert np.array_equal(f.export_u8(mvs.BUF_DISP, lo, hi), oracle.plot_full_image(disp, lo, hi))
+        idx = f.download(mvs.BUF_IDX)
+        for which in (mvs.BUF_STATE_A, mvs.BUF_STATE_B):
+            st = f.download(which)
+            for el in (0, 1, 2):
+                assert np.array_equal(f.export_u8(which, s.min_disp, s.max_disp, element=el),
+                                      oracle.img_translate_state(st, idx, el, s.min_disp, s.max_disp)), (which, el)
+        assert np.array_equal(f.export_u8(mvs.BUF_DISP, 0, 16, v0=2, v1=4), oracle.plot_full_image(disp[2:4], 0, 16))
+    finally:
+        f.close()
