@@ -382,7 +382,9 @@ __global__ void __launch_bounds__(UPD_THREADS) k_update_centers_tiled(const floa
         // position and count sums are exact integers: per lane over all window tiles, one warp
         // reduction at the end.  Per slot the lane adds 1 | k << 8 | nbr_y << 16 (count, row pair, tile row).
         int tx = 0, ty = 0, tn = 0;
-#pragma unroll 1
+        // S = 8: the two live window tiles are unrolled, so the second one (rows 16..23) tests only its four
+        // in-window row pairs
+#pragma unroll(S_T == 8 ? 3 : 1)
         for (int g = 0; g < G; ++g) {
             const int nbr_x = g % cpl, nbr_y = g / cpl;
             if (nbr_y * 16 >= S * 3) break;

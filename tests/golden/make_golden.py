@@ -11,6 +11,9 @@ Cases
   synth_3x2      synthetic piecewise-planar 3x2 array, 96x64, small disparity range
   bar_5x3_crop   160x96 crop of the bundled 15-view set Images/c0f1..c14f1.png (view order of
                  backup/data-bar.txt), shipped literals of clMVDE.cpp:14-36
+  fusion_*       multi-view fusion (project_to_reference_inv + remove_view_inconsistency in the host
+                 sequence of depth_refinement.cpp:1382-1451, disp_proj zero-filled) on the disparity
+                 images of the two pipeline cases above
   slic_*         SLIC only: crops of Images/dance.jpg / horse.jpg, odd sizes, S=8 with
                  connectivity, S=16
 """
@@ -80,10 +83,27 @@ def settings_dict(s):
     return {k: getattr(s, k) for k in s.__dataclass_fields__}
 
 
+def make_fusion(r):
+    """from the committed pipeline goldens, so that it can be regenerated on its own"""
+    import json
+    for src in ("synth_3x2", "bar_5x3_crop"):
+        g = np.load(os.path.join(OUT, src + ".npz"))
+        st = json.loads(str(g["settings"]))
+        disp = g["disp"]
+        assert np.isfinite(disp).all()   # NaN would reproject through an undefined float->int conversion
+        proj, fused = r.view_fusion(disp, st["array_width"], st["bl_ratio"], st["fuse"])
+        np.savez_compressed(os.path.join(OUT, "fusion_" + src + ".npz"), disp=disp, array_width=st["array_width"],
+                            bl_ratio=st["bl_ratio"], fuse=st["fuse"], proj=proj, fused=fused)
+        print("fusion_" + src, "done", flush=True)
+
+
 def main():
     r, o = clref.load(), orc.load()
     assert r is not None, "needs /root/reference (libclref.so)"
     import json
+    if len(sys.argv) > 1 and sys.argv[1] == "fusion":
+        make_fusion(r)
+        return
 
     # 1. synthetic 3x2
     s = mvs.SystemSettings(array_width=3, array_height=2, min_disp=0, max_disp=16, inc=1, bl_ratio=1.0, kernel_size=128)
@@ -112,6 +132,7 @@ def main():
         np.savez_compressed(os.path.join(OUT, name + ".npz"), rgbx=img, S=S, connectivity=conn, weight=0.6, no_iter=5,
                             lab=lab, map=mp, idx=idx)
         print(name, "done", flush=True)
+    make_fusion(r)
 
 
 if __name__ == "__main__":

@@ -115,7 +115,7 @@ def test_restatement_reproduces_slic_golden(oracle, path):
 def test_golden_set_is_present():
     names = {os.path.basename(p) for p in glob.glob(os.path.join(GOLDEN, "*.npz"))}
     assert {"synth_3x2.npz", "bar_5x3_crop.npz", "slic_dance_s8_conn.npz", "slic_horse_s16.npz",
-            "slic_horse_s8.npz"} <= names
+            "slic_horse_s8.npz", "fusion_synth_3x2.npz", "fusion_bar_5x3_crop.npz"} <= names
 
 
 def _fusion_input(seed, aw, ah, W, H, bl):
@@ -141,3 +141,11 @@ def test_view_fusion_restatement_equals_reference_source(oracle, ref, aw, ah, W,
     assert_same(out_o, out_r, "fused disparity")
     # what the stage is for: a fused value is 0 or one of the candidates at that pixel
     assert ((out_o == 0) | (out_o[:, None] == proj_o[None]).any(1)).all()
+
+
+@pytest.mark.parametrize("path", golden_files("fusion_"), ids=os.path.basename)
+def test_restatement_reproduces_view_fusion_golden(oracle, path):
+    g = np.load(path)
+    proj, fused = oracle.view_fusion(g["disp"], int(g["array_width"]), float(g["bl_ratio"]), float(g["fuse"]))
+    assert_same(proj, g["proj"], "disp_proj")
+    assert_same(fused, g["fused"], "fused disparity")

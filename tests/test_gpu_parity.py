@@ -186,6 +186,21 @@ def test_errors_are_loud(ctx):
         mvs.slic_run(ctx, np.zeros((4, 4, 4), np.uint8), S=8)        # image smaller than a superpixel
     with pytest.raises(mvs.MvsError):
         mvs.Context(99)
+    # the additive stages fail the same way
+    f = mvs.Frame(ctx, small_settings(3, 2), 64, 48, 0, 3)             # holds views 0..2 of 6, no communicator
+    try:
+        with pytest.raises(mvs.MvsError, match="every view"):
+            f.view_fusion()
+        with pytest.raises(mvs.MvsError):
+            f.export_u8(mvs.BUF_STATE_A, 0, 16, element=3)
+        with pytest.raises(mvs.MvsError):
+            f.export_u8(mvs.BUF_LAB, 0, 16)
+        with pytest.raises(mvs.MvsError):
+            f.upload_bgr(np.zeros((6, 48, 64, 4), np.uint8))
+    finally:
+        f.close()
+    with pytest.raises(mvs.MvsError):
+        mvs.view_fusion_run(ctx, np.zeros((5, 16, 16), np.float32), 2, 1.0, 1.0)   # 5 views, array width 2
 
 
 # ---- against the golden vectors produced by the reference's own kernel source -------------------
@@ -247,6 +262,14 @@ def _write_ppm(path, rgbx):
     with open(path, "wb") as fh:
         fh.write(b"P6\n%d %d\n255\n" % (w, h))
         fh.write(np.ascontiguousarray(rgbx[..., :3]).tobytes())   # s0=R, s1=G, s2=B
+
+
+@pytest.mark.parametrize("path", _golden("fusion_"), ids=os.path.basename)
+def test_cuda_view_fusion_reproduces_reference_golden(ctx, path):
+    g = np.load(path)
+    proj, fused = mvs.view_fusion_run(ctx, g["disp"], int(g["array_width"]), float(g["bl_ratio"]), float(g["fuse"]))
+    assert_bits_equal(proj, g["proj"], "disp_proj")
+    assert_bits_equal(fused, g["fused"], "fused disparity")
 
 
 @pytest.mark.parametrize("staged", [0, 1])
