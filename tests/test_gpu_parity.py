@@ -378,3 +378,22 @@ def test_export_u8_matches_reference_quantisation(ctx, oracle, small_frame):
         assert np.array_equal(f.export_u8(mvs.BUF_DISP, 0, 16, v0=2, v1=4), oracle.plot_full_image(disp[2:4], 0, 16))
     finally:
         f.close()
+
+
+def test_refinement_with_far_labels(ctx, oracle, small_frame):
+    """hand-made label map: 1 % of the pixels carry the label of an arbitrary, far-away superpixel (SLIC never
+    produces that); the consistency gathers must follow the label wherever it points"""
+    s, rgbx, gt, ref = small_frame
+    idx = ref["idx"].copy()
+    mh, mw = ref["map"].shape[1:3]
+    rng = np.random.default_rng(3)
+    far = rng.random(idx.shape) < 0.01
+    idx[far] = rng.integers(0, mw * mh, size=int(far.sum()), dtype=np.uint32)
+    sub, num = mvs.make_subsets(s.array_width, s.array_height)
+    g, a = np.float32(2 * s.gamma ** 2), np.float32(2 * s.alpha ** 2)
+    want = oracle.refine(ref["map"], idx, ref["rep"], sub, num, s.array_width, s.spixl_size, s.bl_ratio, g, a, s.fuse,
+                         s.kernel_step, s.kernel_size // 2, s.no_prop)
+    got = mvs.refine_run(ctx, ref["map"], idx, ref["rep"], s.spixl_size, s.array_width, s.array_height, s.bl_ratio, sub,
+                         num, g, a, s.fuse, s.kernel_step, s.kernel_size // 2, s.no_prop)
+    for gq, wq, name in zip(got, want, ("flatness", "state A", "state B", "disparity")):
+        assert_bits_equal(gq, wq, name)
