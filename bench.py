@@ -131,8 +131,11 @@ class CpuPath:
     the slab timings are scaled to the frame with a linear model in the neighbour-view count."""
 
     def __init__(self, name):
-        from tests import orc
+        from tests import orc, clref
         self.o = orc.load()
+        # the reference's own kernel source compiled for the CPU (oracle/_ref/libclref.so), when it was built
+        self.r = clref.load() if clref.available() else None
+        self.kind = "reference" if self.r is not None else "port"
         self.s, self.W, self.H, self.rgbx = make_input(name)
         s = self.s
         self.V = s.array_width * s.array_height
@@ -176,11 +179,26 @@ class CpuPath:
         zc = 0                                          # corner view
         ni, nc = int(self.num[zi]), int(self.num[zc])
         T = {}
+        r = self.r
+        S = s.spixl_size
         t = time.perf_counter()
-        o.slic(self.rgbx[k % V], s.spixl_size, s.slic_color_weight, s.no_iter, s.enforce_connectivity)
+        if r is None:
+            o.slic(self.rgbx[k % V], S, s.slic_color_weight, s.no_iter, s.enforce_connectivity)
+        else:
+            # clSLIC::do_super_pixel_seg (clSLIC.cpp:67-122) kernel by kernel from the reference source; only the
+            # centre update runs the port (its 256-work-item barrier has no cheap CPU form)
+            mxy, mcol = o.slic_params(S)
+            lab = r.cvt(self.rgbx[k % V])
+            mp = r.init_centers(lab, S)
+            ix = r.assoc(lab, mp, S, s.slic_color_weight, mxy, mcol)
+            for _ in range(s.no_iter):
+                mp = o.update_centers(lab, ix, mp, S)
+                ix = r.assoc(lab, mp, S, s.slic_color_weight, mxy, mcol)
+            if s.enforce_connectivity:
+                ix = r.suppress(r.suppress(ix))
         T["slic"] = (time.perf_counter() - t) * V
         t = time.perf_counter()
-        o.boundary(self.map, self.idx, s.spixl_size)
+        (r or o).boundary(self.map, self.idx, S)
         T["boundary"] = time.perf_counter() - t
 
         def model(ti, tc):   # t(n) = a + b*n fitted on the interior / corner view, summed over the views
@@ -190,37 +208,46 @@ class CpuPath:
             a = ti - b * ni
             return float(sum(max(a + b * int(n), 0.0) for n in self.num))
 
+        def bm_rows(z):
+            if r is None:
+                o.block_match_rows(self.lab, self.map, self.rep, self.levels, self.sub, self.num, aw, s.bl_ratio, z, y0, y0 + rows)
+            else:
+                r.block_match_rows(self.lab, self.map, self.rep, self.idx, self.levels, self.sub, self.num, aw, s.bl_ratio,
+                                   S, z, y0, y0 + rows)
+
         t = time.perf_counter()
-        o.block_match_rows(self.lab, self.map, self.rep, self.levels, self.sub, self.num, aw, s.bl_ratio, zi, y0, y0 + rows)
+        bm_rows(zi)
         ti = time.perf_counter() - t
         t = time.perf_counter()
-        o.block_match_rows(self.lab, self.map, self.rep, self.levels, self.sub, self.num, aw, s.bl_ratio, zc, y0, y0 + rows)
+        bm_rows(zc)
         tc = time.perf_counter() - t
         T["block_match"] = model(ti, tc) * scale_rows
         t = time.perf_counter()
-        o.flatness(self.map, np.float32(1.0 / float(self.g_)))
+        (r or o).flatness(self.map, np.float32(1.0 / float(self.g_)))
         T["flatness"] = time.perf_counter() - t
         t = time.perf_counter()
-        o.init_state(self.map, self.idx, self.rep, self.flat, self.sub, self.num, aw, s.bl_ratio, self.gam, self.alp,
-                     self.fus, s.kernel_step, self.kss)
+        (r or o).init_state(self.map, self.idx, self.rep, self.flat, self.sub, self.num, aw, s.bl_ratio, self.gam, self.alp,
+                            self.fus, s.kernel_step, self.kss)
         T["init_state"] = time.perf_counter() - t
         T["propagate"] = 0.0
         for it in range(s.no_prop):
             tt = []
             for z in (zi, zc):
                 t = time.perf_counter()
-                o.propagate_rows(self.state, self.scratch, self.map, self.idx, self.rep, self.flat, self.sub, self.num, it,
-                                 aw, s.bl_ratio, self.gam, self.alp, self.fus, s.kernel_step // (it + 1),
-                                 np.float32(self.kss) / np.float32(it + 1), z, y0, y0 + rows)
+                (r or o).propagate_rows(self.state, self.scratch, self.map, self.idx, self.rep, self.flat, self.sub, self.num,
+                                        it, aw, s.bl_ratio, self.gam, self.alp, self.fus, s.kernel_step // (it + 1),
+                                        np.float32(self.kss) / np.float32(it + 1), z, y0, y0 + rows)
                 tt.append(time.perf_counter() - t)
             T["propagate"] += model(tt[0], tt[1]) * scale_rows
         t = time.perf_counter()
-        o.spixl_to_image(self.map, self.idx, self.state)
+        (r or o).spixl_to_image(self.map, self.idx, self.state)
         T["fusion"] = time.perf_counter() - t
         return sum(T.values()), T
 
     def sample_desc(self):
-        return ("CPU oracle (port of clcode.cl), OpenMP: per step SLIC of 1 of %d views (x%d), boundary/flatness/"
+        who = ("the reference's own kernel source (clcode.cl compiled as C++ over a work-item shim, oracle/_ref/libclref.so; "
+               "only update_cluster_center runs the C port)" if self.r is not None else "CPU oracle (port of clcode.cl)")
+        return (who + ", OpenMP over work-items: per step SLIC of 1 of %d views (x%d), boundary/flatness/"
                 "init_state/fusion of all views, and 8 of %d superpixel rows of block matching and of each of the %d "
                 "propagate iterations for one interior and one corner view, scaled by rows and by a linear model in "
                 "the neighbour-view count" % (self.V, self.V, self.map.shape[1], self.s.no_prop))
@@ -250,7 +277,7 @@ def run_reference(args, rank, world):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": frame_s * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args.workload, s, cp.W, cp.H),
-        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cp.cores, "kind": "port",
+        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cp.cores, "kind": cp.kind,
                          "sample": cp.sample_desc()},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "stage_ms": stages, "sample_wall_s_per_step": wall / max(args.steps, 1), "gpu_launches": 0,
@@ -425,7 +452,7 @@ def run_ours(args, rank, world, local_rank):
         if world == 1 and not args.no_cpu:
             cp = CpuPath(args.workload)
             sec, T = cp.step(0)
-            cpu = {"value": 1.0 / sec, "unit": "frames/s", "cores": cp.cores, "kind": "port",
+            cpu = {"value": 1.0 / sec, "unit": "frames/s", "cores": cp.cores, "kind": cp.kind,
                    "sample": cp.sample_desc(), "stage_ms": {k: v * 1e3 for k, v in T.items()}}
         line = {
             "metric": "15-view depth frames/s", "value": value, "unit": "frames/s", "n_gpus": world,

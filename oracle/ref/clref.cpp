@@ -43,6 +43,25 @@ template <class F> static void ndrange(int gx, int gy, int gz, F body)
         }
 }
 
+// the same, restricted to work-items with y in [y0, y1) and z in [z0, z1) of a (gx, gy, gz) NDRange: a
+// bounded SAMPLE of a launch, used only to time the reference's kernels on part of a frame
+template <class F> static void ndrange_part(int gx, int gy, int gz, int y0, int y1, int z0, int z1, F body)
+{
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
+    for (int z = z0; z < z1; ++z)
+        for (int y = y0; y < y1; ++y) {
+            WorkItem &w = wi;
+            w.group_barrier = nullptr;
+            w.gsz[0] = gx; w.gsz[1] = gy; w.gsz[2] = gz;
+            w.lsz[0] = 16; w.lsz[1] = 16; w.lsz[2] = 1;
+            w.gid[1] = y; w.gid[2] = z; w.lid[1] = y % 16; w.lid[2] = 0; w.grp[1] = y / 16; w.grp[2] = z;
+            for (int x = 0; x < gx; ++x) {
+                w.gid[0] = x; w.lid[0] = x % 16; w.grp[0] = x / 16;
+                body();
+            }
+        }
+}
+
 } // namespace clref
 
 using namespace clref;
@@ -167,6 +186,18 @@ void clref_block_match(const void *lab, void *map, const void *rep, const void *
         });
 }
 
+// timing sample: superpixel rows [y0, y1) of view z only
+void clref_block_match_rows(const void *lab, void *map, const void *rep, const void *idx, const float *levels, int nlev,
+                            const int *view_subset, const int *subset_num, int array_width, int V, int W, int H, int mw,
+                            int mh, int S, float bl_ratio, int z, int y0, int y1)
+{
+    int2 isz(W, H), msz(mw, mh);
+    ndrange_part(round_up16(mw), round_up16(mh), 1, y0, y1, 0, 1, [&] {
+        initial_depth_estimation_v2((float3 *)lab, (float8 *)map, (uchar8 *)rep, (clref::uint *)idx, (float *)levels,
+                                    (int *)view_subset, (int *)subset_num, array_width, msz, isz, bl_ratio, S, nlev, V, z);
+    });
+}
+
 // clDepthRefinement::compute_flatness (depth_refinement.cpp:122-147); gamma = the kernel argument
 void clref_flatness(const void *map, void *flat, int V, int mw, int mh, float gamma)
 {
@@ -196,6 +227,20 @@ void clref_propagate(float *state_out, const float *state_in, const void *map, c
 {
     int2 isz(W, H), msz(mw, mh);
     ndrange(round_up16(mw), round_up16(mh), V, [&] {
+        propagate(state_out, (float *)state_in, (float8 *)map, (clref::uint *)idx, (uchar8 *)rep, (float2 *)flat,
+                  (int *)view_subset, (int *)subset_num, iter, msz, isz, alpha, gamma, bl_ratio, fuse, no_kernel_steps,
+                  kernel_step_size, array_width, 1);
+    });
+}
+
+// timing sample: superpixel rows [y0, y1) of view z only (the grid keeps its full size V in z)
+void clref_propagate_rows(float *state_out, const float *state_in, const void *map, const void *idx, const void *rep,
+                          const void *flat, const int *view_subset, const int *subset_num, int iter, int mw, int mh, int W,
+                          int H, float alpha, float gamma, float bl_ratio, float fuse, int no_kernel_steps,
+                          float kernel_step_size, int array_width, int V, int z, int y0, int y1)
+{
+    int2 isz(W, H), msz(mw, mh);
+    ndrange_part(round_up16(mw), round_up16(mh), V, y0, y1, z, z + 1, [&] {
         propagate(state_out, (float *)state_in, (float8 *)map, (clref::uint *)idx, (uchar8 *)rep, (float2 *)flat,
                   (int *)view_subset, (int *)subset_num, iter, msz, isz, alpha, gamma, bl_ratio, fuse, no_kernel_steps,
                   kernel_step_size, array_width, 1);

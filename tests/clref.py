@@ -99,6 +99,26 @@ class ClRef:
                                    _p(subset_num), aw, V, W, H, mw, mh, S, _cf(bl_ratio))
         return mp
 
+    def block_match_rows(self, lab, mp, rep, idx, levels, subset, subset_num, aw, bl_ratio, S, z, y0, y1):
+        """timing helper: superpixel rows [y0,y1) of view z, result written into a copy"""
+        V, H, W, _ = lab.shape
+        mh, mw = mp.shape[1:3]
+        mp = mp.copy()
+        levels = np.ascontiguousarray(levels, f32)
+        self.lib.clref_block_match_rows(_p(lab), _p(mp), _p(rep), _p(idx), _p(levels), len(levels), _p(subset),
+                                        _p(subset_num), aw, V, W, H, mw, mh, S, _cf(bl_ratio), z, y0, y1)
+        return mp
+
+    def propagate_rows(self, st_in, out, mp, idx, rep, flat, subset, subset_num, it, aw, bl_ratio, gamma, alpha, fuse,
+                       ksteps, kss, z, y0, y1):
+        """timing helper: superpixel rows [y0,y1) of view z into `out`"""
+        V, H, W = idx.shape
+        mh, mw = mp.shape[1:3]
+        self.lib.clref_propagate_rows(_p(out), _p(st_in), _p(mp), _p(idx), _p(rep), _p(flat), _p(subset), _p(subset_num),
+                                      it, mw, mh, W, H, _cf(alpha), _cf(gamma), _cf(bl_ratio), _cf(fuse), ksteps, _cf(kss),
+                                      aw, V, z, y0, y1)
+        return out
+
     # ---- refinement (depth_refinement.cpp:91-118)
     def flatness(self, mp, gamma_flat):
         V, mh, mw, _ = mp.shape
