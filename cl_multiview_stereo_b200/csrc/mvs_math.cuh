@@ -22,6 +22,10 @@ __device__ __forceinline__ int d2i(double x) { return __double2int_rz(x); }
 
 // exp(x), binary32: Cody-Waite reduction by ln2 (hi/lo), degree-5 polynomial in
 // Horner form, scaling by two exact powers of two.
+// NONPOS = the caller guarantees x <= 0 or NaN (x = -(d*d)*w with w >= 0): the overflow select can never
+// fire and a NaN argument already leaves y = NaN (every step propagates it), so both selects are dropped --
+// same value for every admissible argument, four instructions fewer.
+template <bool NONPOS = false>
 __device__ __forceinline__ float expf_pinned(float x)
 {
     // branch-free: the polynomial is always evaluated and the three special ranges are selected
@@ -45,8 +49,10 @@ __device__ __forceinline__ float expf_pinned(float x)
     y = y * pow2i(k1);
     y = y * pow2i(k2);
     y = x < -104.0f ? 0.0f : y;
-    y = x > 88.72284f ? __int_as_float(0x7f800000) : y;
-    y = x != x ? x : y;
+    if (!NONPOS) {
+        y = x > 88.72284f ? __int_as_float(0x7f800000) : y;
+        y = x != x ? x : y;
+    }
     return y;
 }
 

@@ -119,7 +119,8 @@ __device__ __forceinline__ bool same_bits(const float4 &p, const float4 &q)
 // UNIT: every neighbour view is at most one camera apart in x and y (neib_hor, neib_ver <= 1).
 // Then round(d * dv) == dv * round(d) exactly (dv in {-1, 0, 1}; holds for inf / NaN too), and
 // the two rounds of a sample are taken once per (plane, sample) instead of once per view.
-template <bool UNIT, int MINB>
+// NP: gamma >= 0 and alpha >= 0 (checked by the launcher), so every exp argument -(d*d)*w is <= 0 or NaN
+template <bool UNIT, int MINB, bool NP>
 __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
 {
     extern __shared__ __align__(16) unsigned char pr_smem[];
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
             if (ok) {
                 const float4 qa = vm[2 * q], qb = vm[2 * q + 1];
                 const float diff = dist3(cL, ca, cb, qa.w, qb.x, qb.y);
-                const float sim = expf_pinned(-diff * diff * g);
+                const float sim = expf_pinned<NP>(-diff * diff * g);
                 tab[T + __popc(m8 & lower8)] = make_float4(cx - qa.y, cy - qa.z, vp[q].x, sim);
             }
             T += __popc(m8);
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                 const float diff = dist3(cL, ca, cb, qa.w, qb.x, qb.y);
                 const int pos = NU + __popc(m8 & lower8);
                 cp[pos] = make_float4(cd, pl.y, pl.z, pl.w);
-                cw[pos] = expf_pinned(-diff * diff * a.gamma);
+                cw[pos] = expf_pinned<NP>(-diff * diff * a.gamma);
             }
             NU += __popc(m8);
         }
@@ -323,10 +324,10 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                             const float d_proj = (pl[j].y * (qcx[j] - fxp[j]) + pl[j].z * (qcy[j] - fyp[j]) + pl[j].w * pl[j].x) / pl[j].w;
                             const float diff = d_proj - dik[j];
                             // visible += when_visible * exp(..): 0 * exp is +0 unless diff is NaN
-                            if (fabsf(diff) < a.fuse) { visible += expf_pinned(-diff * diff * a.alpha); vws += 1.0f; }
+                            if (fabsf(diff) < a.fuse) { visible += expf_pinned<NP>(-diff * diff * a.alpha); vws += 1.0f; }
                             else { if (diff != diff) visible += diff; ows += 1.0f; }
                             const float cdiff = dist3(qL[j], qA[j], qB[j], cL, ca, cb);
-                            visibility += expf_pinned(-cdiff * cdiff * a.gamma);
+                            visibility += expf_pinned<NP>(-cdiff * cdiff * a.gamma);
                             num += 1.0f;
                         }
                 }
@@ -347,7 +348,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                     const float4 e = tab[t];
                     const float d_intrp = (pl.y * e.x + pl.z * e.y + pl.w * pl.x) / pl.w;   // clcode.cl:1426-1428
                     const float diff = d_intrp - e.z;
-                    prod[u * pstride + t] = e.w * expf_pinned(-diff * diff * a.alpha);
+                    prod[u * pstride + t] = e.w * expf_pinned<NP>(-diff * diff * a.alpha);
                 }
             }
             __syncwarp();
@@ -501,13 +502,15 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     // every neighbour at most one camera apart?  (host copy of the lists lives with the frame)
     bool unit = f.unit_baseline != 0;
     dim3 g((f.mw + PR_OCT - 1) / PR_OCT, z1 - z0, (f.mh + PR_WARPS - 1) / PR_WARPS);
-#define PR_LAUNCH(U, B)                                                                                          \
+    const bool np = a.gamma >= 0.0f && a.alpha >= 0.0f;
+#define PR_LAUNCH(U, B, P)                                                                                       \
     do {                                                                                                         \
-        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        k_propagate<U, B><<<g, PR_WARPS * 32, smem, st>>>(a);                                                    \
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        k_propagate<U, B, P><<<g, PR_WARPS * 32, smem, st>>>(a);                                                 \
     } while (0)
-    if (!unit) PR_LAUNCH(false, 5);
-    else PR_LAUNCH(true, 5);
+    if (!unit) { if (np) PR_LAUNCH(false, 5, true); else PR_LAUNCH(false, 5, false); }
+    else if (np) PR_LAUNCH(true, 5, true);
+    else PR_LAUNCH(true, 5, false);
 #undef PR_LAUNCH
     return 1;
 }
