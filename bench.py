@@ -519,28 +519,39 @@ def run_slic_batch(args, rank, world, local_rank):
     ms = max_over_ranks(ctx.event_elapsed_ms(0, 1)) / args.steps
     launches = ctx.launches - l0
     clocks = sampler.stop() if rank == 0 else None
-    # end to end: pinned host images in, labels + centres out, every step
+    # end to end: pinned host images in, labels + centres out, every step; two frames on two streams
+    # alternate so that the copies of one batch overlap the kernels of the other
+    ctx2 = mvs.Context(local_rank)
+    frame2 = mvs.Frame(ctx2, s, W, H)
+    ctxs, frames = [ctx, ctx2], [frame, frame2]
+    for f in frames:
+        f.set_timing(False)
     pin_in = mvs.PinnedBuffer(imgs.shape, np.uint8)
     pin_in.array[...] = imgs
     mw, mh = mvs.map_size(W, H, s.spixl_size)
-    pin_idx = mvs.PinnedBuffer((B, H, W), np.uint32)
-    pin_map = mvs.PinnedBuffer((B, mh, mw, 8), np.float32)
+    pin_idx = [mvs.PinnedBuffer((B, H, W), np.uint32) for _ in range(2)]
+    pin_map = [mvs.PinnedBuffer((B, mh, mw, 8), np.float32) for _ in range(2)]
 
-    def e2e_step():
-        frame.upload(mvs.BUF_RGBX, pin_in.array, sync=False)
-        frame.slic()
-        frame.download(mvs.BUF_IDX, out=pin_idx.array, sync=False)
-        frame.download(mvs.BUF_MAP, out=pin_map.array, sync=False)
+    def e2e_step(i):
+        k = i & 1
+        ctxs[k].sync()
+        frames[k].upload(mvs.BUF_RGBX, pin_in.array, sync=False)
+        frames[k].slic()
+        frames[k].download(mvs.BUF_IDX, out=pin_idx[k].array, sync=False)
+        frames[k].download(mvs.BUF_MAP, out=pin_map[k].array, sync=False)
 
-    for _ in range(2):
-        e2e_step()
-    ctx.sync()
+    for i in range(2):
+        e2e_step(i)
+    ctxs[0].sync(); ctxs[1].sync()
     ctx.event_record(2)
-    for _ in range(args.steps):
-        e2e_step()
+    for i in range(args.steps):
+        e2e_step(i)
+    ctxs[1].sync(); ctxs[0].sync()
     ctx.event_record(3)
     ctx.sync()
     e2e_ms = max_over_ranks(ctx.event_elapsed_ms(2, 3)) / args.steps
+    pin_idx, pin_map = pin_idx[(args.steps - 1) & 1], pin_map[(args.steps - 1) & 1]
+    frame2.close(); ctx2.close()
     if rank == 0:
         peak = 6650.0
         try:

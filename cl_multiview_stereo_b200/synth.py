@@ -41,22 +41,31 @@ def make_scene(seed, W, H, n_patches=12, dmin=32.0, dmax=58.0):
 def render_view(scene, gx, gy, bl_ratio=1.0):
     """view at grid position (gx, gy) -> (rgbx uint8 [H,W,4] with s0=R,s1=G,s2=B, gt disparity float32 [H,W])"""
     W, H, pad = scene["W"], scene["H"], scene["pad"]
-    ys, xs = np.mgrid[0:H, 0:W].astype(np.float32)
     rgb = np.zeros((H, W, 3), np.uint8)
     gt = np.zeros((H, W), np.float32)
     for L in scene["layers"]:   # painter's order: later layers are nearer
         a, b, c = np.float32(L["a"]), np.float32(L["b"]), np.float32(L["c"])
         den = np.float32(1.0) - a * np.float32(gx) - b * np.float32(bl_ratio * gy)
+        x0, y0, x1, y1 = L["rect"]
+        # only the part of the view the layer can reach: its disparity is planar, so the extremes over the
+        # frame sit at the corners (a conservative box; the mask below decides pixel by pixel)
+        dc = [(float(a) * cx + float(b) * cy + float(c)) / float(den) for cx in (0, W - 1) for cy in (0, H - 1)]
+        dlo, dhi = min(dc), max(dc)
+        sx, sy = [dlo * gx, dhi * gx], [dlo * bl_ratio * gy, dhi * bl_ratio * gy]
+        bx0 = int(max(0, np.floor(x0 - max(sx)) - 2)); bx1 = int(min(W, np.ceil(x1 - min(sx)) + 3))
+        by0 = int(max(0, np.floor(y0 - max(sy)) - 2)); by1 = int(min(H, np.ceil(y1 - min(sy)) + 3))
+        if bx1 <= bx0 or by1 <= by0:
+            continue
+        ys, xs = np.mgrid[by0:by1, bx0:bx1].astype(np.float32)
         d = (a * xs + b * ys + c) / den
         xr = xs + d * np.float32(gx)
         yr = ys + d * np.float32(bl_ratio * gy)
-        x0, y0, x1, y1 = L["rect"]
         m = (xr >= x0) & (xr < x1) & (yr >= y0) & (yr < y1)
         xi = np.clip(np.rint(xr).astype(np.int32) + pad, 0, W + 2 * pad - 1)
         yi = np.clip(np.rint(yr).astype(np.int32) + pad, 0, H + 2 * pad - 1)
         col = L["tex"][yi, xi]
-        rgb[m] = col[m]
-        gt[m] = d[m]
+        rgb[by0:by1, bx0:bx1][m] = col[m]
+        gt[by0:by1, bx0:bx1][m] = d[m]
     rgbx = np.zeros((H, W, 4), np.uint8)
     rgbx[..., :3] = rgb
     return rgbx, gt
