@@ -282,6 +282,8 @@ static int set_tables(mvs_frame *f, const int *subset, const int *subset_num, co
             if (subset[z * V + k] < 0 || subset[z * V + k] >= V) return fail("view_subset[%d][%d] out of range", z, k);
     }
     f->d.unit_baseline = 1;
+    f->d.max_neighbours = 1;
+    for (int z = 0; z < V; ++z) f->d.max_neighbours = std::max(f->d.max_neighbours, subset_num[z]);
     for (int z = 0; z < V; ++z)
         for (int k = 0; k < subset_num[z]; ++k) {
             const int v = subset[z * V + k], aw = f->d.aw;

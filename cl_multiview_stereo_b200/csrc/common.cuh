@@ -29,6 +29,7 @@ struct FrameDev {
     float *levels;      // [L]
     int num_levels;
     int unit_baseline;  // every neighbour view at most one camera apart in x and y
+    int max_neighbours; // largest subset_num over the views
 };
 
 struct SlicArgs {

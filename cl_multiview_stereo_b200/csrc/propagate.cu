@@ -29,6 +29,7 @@
 #include "common.cuh"
 #include "mvs_math.cuh"
 #include <stdlib.h>
+#include <algorithm>
 
 namespace mvs {
 
@@ -56,6 +57,7 @@ struct PArgs {
     int iter, z0;
     int tmax;                 // smoothness terms per superpixel at most (8 + 4K)
     int ncmax;                // candidate slots per superpixel at most (valid neighbours + far + 8 pairs)
+    int nsmax;                // neighbour views per view at most (8 on a grid with neib_hor = neib_ver = 1)
 };
 
 // shared-memory record of one superpixel (dynamic part sized by tmax / ncmax)
@@ -63,14 +65,14 @@ struct SpLayout {
     int tab, cp, cc, cw, own, uniq, sres, stage, total;
 };
 
-__host__ __device__ inline SpLayout sp_layout(int tmax, int ncmax)
+__host__ __device__ inline SpLayout sp_layout(int tmax, int ncmax, int nsmax)
 {
     SpLayout L;
-    int o = 9 * 16 + 8 * 16;                  // samp[9], viewt[8]
+    int o = 9 * 16 + nsmax * 16;              // samp[9], viewt[nsmax]
     L.tab = o;   o += 16 * tmax;              // float4 tab[tmax]
     L.cp = o;    o += 16 * ncmax;             // float4 candidate planes
     L.cc = o;    o += 8 * ncmax;              // float2 costs of the unique ones
-    L.sres = o;  o += 8 * PR_UB * 8;          // float2 per (plane, view): {term, flags}
+    L.sres = o;  o += 8 * PR_UB * nsmax;      // float2 per (plane, view): {term, flags}
     const int prod_bytes = 4 * PR_UB * (tmax + 1), sdi_bytes = 16 * PR_UB * 9;
     L.stage = o; o += ((prod_bytes > sdi_bytes ? prod_bytes : sdi_bytes) + 15) & ~15;   // sdi (E,F) then prod (G,H)
     L.cw = o;    o += 4 * ncmax;              // float acceptance weight (colour similarity to the source)
@@ -133,7 +135,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     const int x = blockIdx.x * PR_OCT + (lane >> 3), y = blockIdx.z * PR_WARPS + warp, z = a.z0 + blockIdx.y;
     const bool live = x < a.mw && y < a.mh;
 
-    const SpLayout L = sp_layout(a.tmax, a.ncmax);
+    const SpLayout L = sp_layout(a.tmax, a.ncmax, a.nsmax);
     unsigned char *sbase = pr_smem + (size_t)(warp * PR_OCT + (lane >> 3)) * L.total;
     float4 *samp = reinterpret_cast<float4 *>(sbase);            // {sx, sy (integers held as float), cx - sx, cy - sy}
     float4 *viewt = samp + 9;                                    // {view * N (int bits), dvx, dvy, view * M (int bits)}
@@ -159,7 +161,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     const int ns = live ? a.subset_num[z] : 0;
     const int camx = z % a.aw, camy = z / a.aw;
     const double half_fly = 0.5 * (double)fl.y;   // clcode.cl:1621 is a double expression
-    const unsigned ns_inv = 65536u / (unsigned)max(ns, 1) + 1u;   // p / ns for p < 64
+    const unsigned ns_inv = 65536u / (unsigned)max(ns, 1) + 1u;   // p / ns for p < PR_UB * ns <= 1024
 
     // sample table: sample k = (i+1)*3 + (j+1) sits s_k pixels along ray (i, j) from the
     // truncated centre (clcode.cl:1547-1566); rep bytes are {nw,w,sw,n,s,ne,e,se}
@@ -173,10 +175,10 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
             // |sx|, |sy| < 2^24: the float copies are exact
             samp[k] = make_float4((float)sx, (float)sy, cx - (float)sx, cy - (float)sy);
         }
-        if (l8 < ns) {
-            int view = a.view_subset[a.V * z + l8];
-            viewt[l8] = make_float4(__int_as_float(view * a.N), (float)(view % a.aw - camx),
-                                    (float)(view / a.aw - camy), __int_as_float(view * a.M));
+        for (int n = l8; n < ns; n += 8) {
+            int view = a.view_subset[a.V * z + n];
+            viewt[n] = make_float4(__int_as_float(view * a.N), (float)(view % a.aw - camx),
+                                   (float)(view / a.aw - camy), __int_as_float(view * a.M));
         }
     }
 
@@ -338,7 +340,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                     if (vws > 0.0f) { flags |= 2; term = (vws / num) * (visibility / vws) * (visible / vws); }
                     if (ows > 0.0f) flags |= 4;
                 }
-                sres[u * 8 + n] = make_float2(term, __int_as_float(flags));
+                sres[u * a.nsmax + n] = make_float2(term, __int_as_float(flags));
             }
             __syncwarp();   // sdi is dead from here on: prod reuses its storage
             // G: compute_smoothness products, terms spread over the octet
@@ -357,7 +359,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                 float consistency = 0.0f;
                 int view_counter = 0;
                 for (int n = 0; n < ns; ++n) {   // clcode.cl:1614-1622
-                    const float2 rn = sres[l8 * 8 + n];
+                    const float2 rn = sres[l8 * a.nsmax + n];
                     const int fn = __float_as_int(rn.y);
                     if (fn & 1) {
                         view_counter++;
@@ -496,7 +498,8 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
         }
     a.ncmax = nc;
     if (a.ncmax > 255) return -1;   // slot numbers are kept in bytes
-    const SpLayout L = sp_layout(a.tmax, a.ncmax);
+    a.nsmax = std::max(1, f.max_neighbours);
+    const SpLayout L = sp_layout(a.tmax, a.ncmax, a.nsmax);
     size_t smem = (size_t)PR_SPB * L.total;
     if (smem > 227 * 1024 || (double)f.V * f.N >= 2147483648.0) return -1;
     // every neighbour at most one camera apart?  (host copy of the lists lives with the frame)

@@ -47,19 +47,20 @@ template <class F> static void ndrange(int gx, int gy, int gz, F body)
 // bounded SAMPLE of a launch, used only to time the reference's kernels on part of a frame
 template <class F> static void ndrange_part(int gx, int gy, int gz, int y0, int y1, int z0, int z1, F body)
 {
-#pragma omp parallel for collapse(2) schedule(dynamic, 1)
-    for (int z = z0; z < z1; ++z)
-        for (int y = y0; y < y1; ++y) {
-            WorkItem &w = wi;
-            w.group_barrier = nullptr;
-            w.gsz[0] = gx; w.gsz[1] = gy; w.gsz[2] = gz;
-            w.lsz[0] = 16; w.lsz[1] = 16; w.lsz[2] = 1;
-            w.gid[1] = y; w.gid[2] = z; w.lid[1] = y % 16; w.lid[2] = 0; w.grp[1] = y / 16; w.grp[2] = z;
+    // a sample is a few rows: parallel over the work-items of a row as well, so that every core has work
+    for (int z = z0; z < z1; ++z) {
+#pragma omp parallel for collapse(2) schedule(dynamic, 4)
+        for (int y = y0; y < y1; ++y)
             for (int x = 0; x < gx; ++x) {
+                WorkItem &w = wi;
+                w.group_barrier = nullptr;
+                w.gsz[0] = gx; w.gsz[1] = gy; w.gsz[2] = gz;
+                w.lsz[0] = 16; w.lsz[1] = 16; w.lsz[2] = 1;
+                w.gid[1] = y; w.gid[2] = z; w.lid[1] = y % 16; w.lid[2] = 0; w.grp[1] = y / 16; w.grp[2] = z;
                 w.gid[0] = x; w.lid[0] = x % 16; w.grp[0] = x / 16;
                 body();
             }
-        }
+    }
 }
 
 } // namespace clref

@@ -56,18 +56,20 @@ def test_slic_restatement_equals_reference_source(oracle, ref, W, H, S, conn, it
     assert_same(mp_o, mp_r, "spixl_map")
 
 
-@pytest.mark.parametrize("aw,ah,W,H,bl,levels,ksize", [(3, 2, 96, 64, 1.0, (0, 16, 1), 128), (2, 2, 77, 53, 0.625, (2, 40, 2), 64),
-                                                       (5, 3, 64, 48, 1.0359, (0, 12, 1), 1080)])
-def test_depth_restatement_equals_reference_source(oracle, ref, aw, ah, W, H, bl, levels, ksize):
+@pytest.mark.parametrize("aw,ah,W,H,bl,levels,ksize,nh,nv", [
+    (3, 2, 96, 64, 1.0, (0, 16, 1), 128, 1, 1), (2, 2, 77, 53, 0.625, (2, 40, 2), 64, 1, 1),
+    (5, 3, 64, 48, 1.0359, (0, 12, 1), 1080, 1, 1),
+    (5, 3, 64, 48, 1.0, (0, 10, 1), 128, 2, 1), (4, 4, 56, 40, 1.0, (0, 10, 1), 128, 2, 2)])   # > 8 neighbours, wide baselines
+def test_depth_restatement_equals_reference_source(oracle, ref, aw, ah, W, H, bl, levels, ksize, nh, nv):
     """block matching, flatness, init state, every propagate iteration, fusion"""
     s = mvs.SystemSettings(array_width=aw, array_height=ah, min_disp=levels[0], max_disp=levels[1], inc=levels[2],
-                           bl_ratio=bl, kernel_size=ksize)
+                           bl_ratio=bl, kernel_size=ksize, neib_hor=nh, neib_ver=nv)
     rgbx, _ = synth.make_frame(aw * 10 + ah, W, H, aw, ah, bl_ratio=bl, n_patches=4, dmin=levels[0] + 2,
                                dmax=min(levels[1] - 2, 14))
     o = oracle.pipeline(rgbx, s)          # SLIC by the restatement (checked against the source above)
     S = s.spixl_size
     lv = oracle.make_levels(s.min_disp, s.max_disp, s.inc)
-    sub, num = oracle.make_subsets(aw, ah)
+    sub, num = oracle.make_subsets(aw, ah, nh, nv)
     assert_same(o["rep"], ref.boundary(o["map_slic"], o["idx"], S), "spixl_rep")
     assert_same(o["map"], ref.block_match(o["lab"], o["map_slic"], o["rep"], o["idx"], lv, sub, num, aw, bl, S), "initD")
     g_, a_ = np.float32(2 * s.gamma ** 2), np.float32(2 * s.alpha ** 2)

@@ -397,3 +397,23 @@ def test_refinement_with_far_labels(ctx, oracle, small_frame):
                          num, g, a, s.fuse, s.kernel_step, s.kernel_size // 2, s.no_prop)
     for gq, wq, name in zip(got, want, ("flatness", "state A", "state B", "disparity")):
         assert_bits_equal(gq, wq, name)
+
+
+@pytest.mark.parametrize("aw,ah,nh,nv,W,H", [(5, 3, 2, 1, 128, 96), (4, 4, 2, 2, 96, 64), (5, 1, 4, 0, 96, 64)])
+def test_wide_neighbourhoods_match_oracle(ctx, oracle, aw, ah, nh, nv, W, H):
+    """neib_hor / neib_ver > 1 (pipeline.cpp:130-142): more than eight neighbour views per view and
+    baselines of several cameras, i.e. the general reprojection path of propagate (round(d * dv) per view)"""
+    s = small_settings(aw, ah, neib_hor=nh, neib_ver=nv, max_disp=10)
+    rgbx, gt = synth.make_frame(5, W, H, aw, ah, bl_ratio=1.0, n_patches=4, dmin=2, dmax=8)
+    ref = oracle.pipeline(rgbx, s)
+    f = mvs.Frame(ctx, s, W, H)
+    try:
+        f.upload(mvs.BUF_RGBX, rgbx)
+        f.run()
+        assert np.array_equal(f.download(mvs.BUF_IDX), ref["idx"])
+        assert_bits_equal(f.download(mvs.BUF_MAP), ref["map"], "map (initial disparities)")
+        assert_bits_equal(f.download(mvs.BUF_STATE_A), ref["state_a"], "state A")
+        assert_bits_equal(f.download(mvs.BUF_STATE_B), ref["state_b"], "state B")
+        assert_bits_equal(f.download(mvs.BUF_DISP), ref["disp"], "disparity")
+    finally:
+        f.close()
