@@ -690,7 +690,10 @@ extern "C" int mvs_frame_propagate(mvs_frame *f, int iter)
     // per-iteration arguments, depth_refinement.cpp:768-769 (int / int, float / int)
     RefineArgs a{f->gamma, f->alpha, f->fuse, f->bl_ratio, f->kernel_step / (iter + 1), f->kss / (float)(iter + 1), iter};
     int nl = launch_propagate(f->d, a, src, dst, f->lo, f->hi, f->ctx->stream);
-    if (nl < 0) return fail("propagate: kernel_step %d needs more shared memory than one SM has", a.no_kernel_steps);
+    if (nl == -3) return fail("propagate: %d views of %d pixels exceed the 2^31 pixels one frame may hold", f->d.V, f->d.N);
+    if (nl == -2) return fail("propagate: kernel_step %d gives more than 255 candidate planes per superpixel", a.no_kernel_steps);
+    if (nl < 0) return fail("propagate: kernel_step %d with %d neighbour views needs more shared memory than one SM has",
+                            a.no_kernel_steps, f->d.max_neighbours);
     f->ctx->launches += nl;
     return check_launch("propagate");
 }

@@ -62,13 +62,14 @@ struct PArgs {
 
 // shared-memory record of one superpixel (dynamic part sized by tmax / ncmax)
 struct SpLayout {
-    int tab, cp, cc, cw, own, uniq, sres, stage, total;
+    int meta, tab, cp, cc, cw, own, uniq, sres, stage, total;
 };
 
 __host__ __device__ inline SpLayout sp_layout(int tmax, int ncmax, int nsmax)
 {
     SpLayout L;
     int o = 9 * 16 + nsmax * 16;              // samp[9], viewt[nsmax]
+    L.meta = o;  o += 16;                     // {L, a, b} of the own centre (read by whichever lane samples for it)
     L.tab = o;   o += 16 * tmax;              // float4 tab[tmax]
     L.cp = o;    o += 16 * ncmax;             // float4 candidate planes
     L.cc = o;    o += 8 * ncmax;              // float2 costs of the unique ones
@@ -158,10 +159,12 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     const float4 ma = vm[2 * sp], mb = vm[2 * sp + 1];
     const float cx = ma.y, cy = ma.z, cL = ma.w, ca = mb.x, cb = mb.y;
     const float2 fl = a.flat[zM + sp];
+    if (l8 == 0) *reinterpret_cast<float4 *>(sbase + L.meta) = make_float4(cL, ca, cb, 0.0f);
     const int ns = live ? a.subset_num[z] : 0;
     const int camx = z % a.aw, camy = z / a.aw;
     const double half_fly = 0.5 * (double)fl.y;   // clcode.cl:1621 is a double expression
-    const unsigned ns_inv = 65536u / (unsigned)max(ns, 1) + 1u;   // p / ns for p < PR_UB * ns <= 1024
+    const int nsw = a.subset_num[z];   // warp-uniform (ns is 0 for octets outside the map)
+    const unsigned nsw_inv = 65536u / (unsigned)max(nsw, 1) + 1u;   // p / nsw for p < PR_UB * nsw <= 1024
 
     // sample table: sample k = (i+1)*3 + (j+1) sits s_k pixels along ray (i, j) from the
     // truncated centre (clcode.cl:1547-1566); rep bytes are {nw,w,sw,n,s,ne,e,se}
@@ -280,9 +283,21 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
             }
             __syncwarp();
             // F: compute_consistency, one lane per (plane, neighbour view), samples in order
-            for (int p = l8; p < nb * ns; p += 8) {
-                const int u = (int)(((unsigned)p * ns_inv) >> 16), n = p - u * ns;
-                const float4 vt = viewt[n];
+            // The (plane, view) items of the four octets are pooled over the 32 lanes of the warp: an octet with
+            // few unique planes lends its lanes to the others (all octets of a CTA belong to one view: same ns).
+            const int e0 = __shfl_sync(FULL, nb, 0) * nsw, e1 = e0 + __shfl_sync(FULL, nb, 8) * nsw;
+            const int e2 = e1 + __shfl_sync(FULL, nb, 16) * nsw, e3 = e2 + __shfl_sync(FULL, nb, 24) * nsw;
+            for (int it = lane; it < e3; it += 32) {
+                const int oc = (it >= e0) + (it >= e1) + (it >= e2);
+                const int p = it - (oc == 0 ? 0 : oc == 1 ? e0 : oc == 2 ? e1 : e2);
+                const int u = (int)(((unsigned)p * nsw_inv) >> 16), n = p - u * nsw;
+                const unsigned char *ob = pr_smem + (size_t)(warp * PR_OCT + oc) * L.total;
+                const float4 *samp = reinterpret_cast<const float4 *>(ob);
+                const float4 *sdi = reinterpret_cast<const float4 *>(ob + L.stage);
+                float2 *sres = reinterpret_cast<float2 *>(const_cast<unsigned char *>(ob) + L.sres);
+                const float4 own = *reinterpret_cast<const float4 *>(ob + L.meta);
+                const float cL = own.x, ca = own.y, cb = own.z;
+                const float4 vt = samp[9 + n];   // that octet's view table (an octet outside the map has none)
                 const uint32_t nbase = (uint32_t)__float_as_int(vt.x), mbase = (uint32_t)__float_as_int(vt.w);
                 float num = 0.0f, vws = 0.0f, ows = 0.0f, visibility = 0.0f, visible = 0.0f;
                 // three samples at a time: their label gathers, then their centre / plane gathers, are
@@ -497,11 +512,12 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
             if (off < f.mw - 1) nc += 2;
         }
     a.ncmax = nc;
-    if (a.ncmax > 255) return -1;   // slot numbers are kept in bytes
+    if (a.ncmax > 255) return -2;   // slot numbers are kept in bytes
     a.nsmax = std::max(1, f.max_neighbours);
     const SpLayout L = sp_layout(a.tmax, a.ncmax, a.nsmax);
     size_t smem = (size_t)PR_SPB * L.total;
-    if (smem > 227 * 1024 || (double)f.V * f.N >= 2147483648.0) return -1;
+    if ((double)f.V * f.N >= 2147483648.0) return -3;   // 32-bit gather offsets
+    if (smem > 227 * 1024) return -1;
     // every neighbour at most one camera apart?  (host copy of the lists lives with the frame)
     bool unit = f.unit_baseline != 0;
     dim3 g((f.mw + PR_OCT - 1) / PR_OCT, z1 - z0, (f.mh + PR_WARPS - 1) / PR_WARPS);
