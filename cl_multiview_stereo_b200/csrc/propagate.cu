@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     const int camx = z % a.aw, camy = z / a.aw;
     const double half_fly = 0.5 * (double)fl.y;   // clcode.cl:1621 is a double expression
     const int nsw = a.subset_num[z];   // warp-uniform (ns is 0 for octets outside the map)
-    const unsigned nsw_inv = 65536u / (unsigned)max(nsw, 1) + 1u;   // p / nsw for p < PR_UB * nsw <= 1024
+    const unsigned nsw_inv = 16777216u / (unsigned)max(nsw, 1) + 1u;   // p / nsw == (p * nsw_inv) >> 24 for p * nsw < 2^24
 
     // sample table: sample k = (i+1)*3 + (j+1) sits s_k pixels along ray (i, j) from the
     // truncated centre (clcode.cl:1547-1566); rep bytes are {nw,w,sw,n,s,ne,e,se}
@@ -285,12 +285,13 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
             // F: compute_consistency, one lane per (plane, neighbour view), samples in order
             // The (plane, view) items of the four octets are pooled over the 32 lanes of the warp: an octet with
             // few unique planes lends its lanes to the others (all octets of a CTA belong to one view: same ns).
-            const int e0 = __shfl_sync(FULL, nb, 0) * nsw, e1 = e0 + __shfl_sync(FULL, nb, 8) * nsw;
-            const int e2 = e1 + __shfl_sync(FULL, nb, 16) * nsw, e3 = e2 + __shfl_sync(FULL, nb, 24) * nsw;
+            const int nb0 = __shfl_sync(FULL, nb, 0), nb1 = __shfl_sync(FULL, nb, 8);
+            const int nb2 = __shfl_sync(FULL, nb, 16), nb3 = __shfl_sync(FULL, nb, 24);
+            const int e0 = nb0 * nsw, e1 = e0 + nb1 * nsw, e2 = e1 + nb2 * nsw, e3 = e2 + nb3 * nsw;
             for (int it = lane; it < e3; it += 32) {
                 const int oc = (it >= e0) + (it >= e1) + (it >= e2);
                 const int p = it - (oc == 0 ? 0 : oc == 1 ? e0 : oc == 2 ? e1 : e2);
-                const int u = (int)(((unsigned)p * nsw_inv) >> 16), n = p - u * nsw;
+                const int u = (int)(((unsigned long long)(unsigned)p * nsw_inv) >> 24), n = p - u * nsw;
                 const unsigned char *ob = pr_smem + (size_t)(warp * PR_OCT + oc) * L.total;
                 const float4 *samp = reinterpret_cast<const float4 *>(ob);
                 const float4 *sdi = reinterpret_cast<const float4 *>(ob + L.stage);
@@ -358,7 +359,8 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                 sres[u * a.nsmax + n] = make_float2(term, __int_as_float(flags));
             }
             __syncwarp();   // sdi is dead from here on: prod reuses its storage
-            // G: compute_smoothness products, terms spread over the octet
+            // G: compute_smoothness products, terms spread over the octet (pooling these over the warp like the
+            // consistency items costs more in index arithmetic than it saves: 15.2 -> 15.8 ms)
             for (int u = 0; u < nb; ++u) {
                 const float4 pl = cp[uniq[b0 + u]];
                 for (int t = l8; t < T; t += 8) {
