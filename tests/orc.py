@@ -194,6 +194,18 @@ class Oracle:
         self.lib.orc_view_fusion(_p(disp), _p(proj), _p(out), V, W, H, aw, _cf(bl_ratio), _cf(fuse_))
         return proj, out
 
+    def project_inv(self, disp, proj, ref, aw, bl_ratio):
+        """kernel project_to_reference_inv for one reference view, in place into proj[ref]"""
+        V, H, W = disp.shape
+        self.lib.orc_project_to_reference_inv(_p(disp), _p(proj), int(ref), V, W, H, aw, _cf(bl_ratio))
+
+    def remove_inconsistency(self, proj, disp, out, ref, aw, bl_ratio, fuse_kernel):
+        """kernel remove_view_inconsistency for one reference view, in place into out[ref]; fuse_kernel is the
+        kernel argument (0.5 * system_settings::fuse)"""
+        V, H, W = disp.shape
+        self.lib.orc_remove_view_inconsistency(_p(proj), _p(disp), _p(out), int(ref), V, W, H, aw, _cf(bl_ratio),
+                                               _cf(fuse_kernel))
+
     # ---- host-side byte work (file_handler.cpp:6-15, depth_refinement.cpp:1476-1560)
     def load_image_in(self, bgr):
         bgr = np.ascontiguousarray(bgr, u8)

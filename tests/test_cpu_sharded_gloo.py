@@ -122,8 +122,35 @@ def _worker(rank, world, port, out_dir):
         nxt[poison] = np.nan
         states.append(nxt[lo:hi].copy())
         st = nxt
+    # multi-view fusion on the sharded frame (mvs_frame_view_fusion): own disparity images, every rank sends its
+    # own to every other rank, chases the slices 0..hi-1 itself and votes its own views in view order
+    st_a = states[s.no_prop - 1] if s.no_prop % 2 == 0 else states[s.no_prop - 2]   # fusion reads buffer A
+    st_full = np.full((V, mh, mw, 6), np.nan, np.float32)
+    st_full[lo:hi] = st_a
+    disp = np.zeros((V, H, W), np.float32)
+    disp[lo:hi] = o.spixl_to_image(mp, idx, st_full)[lo:hi]
+    reqs, bufs = [], []
+    for r in range(world):
+        if r == rank:
+            continue
+        rlo, rhi = mvs.view_partition(V, world, r)
+        if hi > lo:
+            reqs.append(dist.isend(torch.from_numpy(disp[lo:hi].reshape(-1).copy()), r, tag=1000 + rank))
+        if rhi > rlo:
+            t = torch.empty((rhi - rlo) * H * W, dtype=torch.float32)
+            bufs.append((rlo, rhi, t))
+            reqs.append(dist.irecv(t, r, tag=1000 + r))
+    for q in reqs:
+        q.wait()
+    for rlo, rhi, t in bufs:
+        disp[rlo:rhi] = t.numpy().reshape(rhi - rlo, H, W)
+    proj, fused = np.zeros_like(disp), np.zeros_like(disp)
+    for r in range(hi):
+        o.project_inv(disp, proj, r, AW, s.bl_ratio)
+        if r >= lo:
+            o.remove_inconsistency(proj, disp, fused, r, AW, s.bl_ratio, 0.5 * s.fuse)
     np.savez(os.path.join(out_dir, f"rank{rank}.npz"), lo=lo, hi=hi, idx=idx[lo:hi], map=mp[lo:hi],
-             states=np.stack(states), halo=np.array(halo))
+             states=np.stack(states), halo=np.array(halo), disp=disp[lo:hi], fused=fused[lo:hi])
     dist.barrier()
     dist.destroy_process_group()
 
@@ -149,6 +176,7 @@ def test_view_sharded_over_gloo_equals_single_process(oracle, tmp_path):
         st = oracle.propagate(st, ref["map"], ref["idx"], ref["rep"], ref["flat"], sub, num, it, AW, s.bl_ratio, gam, alp,
                               fus, s.kernel_step // (it + 1), np.float32(kss) / np.float32(it + 1))
         full_states.append(st)
+    proj_full, fused_full = oracle.view_fusion(ref["disp"], AW, s.bl_ratio, s.fuse)
     seen = 0
     for r in range(world):
         d = np.load(tmp_path / f"rank{r}.npz")
@@ -161,5 +189,8 @@ def test_view_sharded_over_gloo_equals_single_process(oracle, tmp_path):
         for it in range(s.no_prop):
             assert np.array_equal(d["states"][it].view(np.uint32), full_states[it][lo:hi].view(np.uint32)), \
                 f"rank {r}: state after iteration {it} differs from the single-process run"
+        assert np.array_equal(d["disp"].view(np.uint32), ref["disp"][lo:hi].view(np.uint32))
+        assert np.array_equal(d["fused"].view(np.uint32), fused_full[lo:hi].view(np.uint32)), \
+            f"rank {r}: sharded multi-view fusion differs from the single-process run"
         seen += hi - lo
     assert seen == V

@@ -10,7 +10,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 TAG=$T bash tools/ncu_frame.sh > gpurun_out/capture_frame_$T.log 2>&1
 B="python bench.py --steps 1 --warmup 3 --no-cpu"
 for k in k_propagate k_block_match; do
-  timeout 400 ncu --set full --clock-control none --import-source on -k regex:$k -s 8 -c 1 -o gpurun_out/r01_${T}_$k $B > gpurun_out/ncu_$k.log 2>&1
+  timeout 400 ncu --set full --clock-control none --import-source on -k regex:$k -s 2 -c 1 -o gpurun_out/r01_${T}_$k $B > gpurun_out/ncu_$k.log 2>&1
   ncu -i gpurun_out/r01_${T}_$k.ncu-rep --page source --csv > gpurun_out/r01_${T}_$k.source.csv 2>/dev/null
   ncu -i gpurun_out/r01_${T}_$k.ncu-rep --page details > gpurun_out/r01_${T}_$k.details.txt 2>/dev/null
 done
