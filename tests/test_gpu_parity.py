@@ -137,7 +137,8 @@ def test_refinement_per_iteration(ctx, oracle, small_frame):
         f.close()
 
 
-@pytest.mark.parametrize("aw,ah,W,H,seed", [(3, 2, 192, 128, 7), (2, 2, 141, 94, 3), (5, 3, 128, 96, 11)])
+@pytest.mark.parametrize("aw,ah,W,H,seed", [(3, 2, 192, 128, 7), (2, 2, 141, 94, 3), (5, 3, 128, 96, 11),
+                                              (1, 1, 96, 64, 9)])   # a single view: no neighbour at all (Appendix B B9)
 def test_full_pipeline_matches_oracle(ctx, oracle, aw, ah, W, H, seed):
     s = small_settings(aw, ah)
     rgbx, gt = synth.make_frame(seed, W, H, aw, ah, bl_ratio=1.0, n_patches=5, dmin=4, dmax=14)
