@@ -164,7 +164,6 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     const int camx = z % a.aw, camy = z / a.aw;
     const double half_fly = 0.5 * (double)fl.y;   // clcode.cl:1621 is a double expression
     const int nsw = a.subset_num[z];   // warp-uniform (ns is 0 for octets outside the map)
-    const unsigned nsw_inv = 16777216u / (unsigned)max(nsw, 1) + 1u;   // p / nsw == (p * nsw_inv) >> 24 for p * nsw < 2^24
 
     // sample table: sample k = (i+1)*3 + (j+1) sits s_k pixels along ray (i, j) from the
     // truncated centre (clcode.cl:1547-1566); rep bytes are {nw,w,sw,n,s,ne,e,se}
@@ -287,11 +286,15 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
             // few unique planes lends its lanes to the others (all octets of a CTA belong to one view: same ns).
             const int nb0 = __shfl_sync(FULL, nb, 0), nb1 = __shfl_sync(FULL, nb, 8);
             const int nb2 = __shfl_sync(FULL, nb, 16), nb3 = __shfl_sync(FULL, nb, 24);
-            const int e0 = nb0 * nsw, e1 = e0 + nb1 * nsw, e2 = e1 + nb2 * nsw, e3 = e2 + nb3 * nsw;
-            for (int it = lane; it < e3; it += 32) {
-                const int oc = (it >= e0) + (it >= e1) + (it >= e2);
-                const int p = it - (oc == 0 ? 0 : oc == 1 ? e0 : oc == 2 ? e1 : e2);
-                const int u = (int)(((unsigned long long)(unsigned)p * nsw_inv) >> 24), n = p - u * nsw;
+            // Items are ordered VIEW-major over the whole warp: neighbouring lanes walk the planes of the four
+            // (adjacent) superpixels in the SAME neighbour view, so their label / record / plane gathers fall into
+            // the same few cache lines (15.2 -> 14.7 ms per frame when done per octet, further when done per warp).
+            const int q1 = nb0 + nb1, q2 = q1 + nb2, nbt = q2 + nb3;
+            const unsigned nbt_inv = 16777216u / (unsigned)max(nbt, 1) + 1u;   // it / nbt == (it * nbt_inv) >> 24, it * nbt < 2^24
+            for (int it = lane; it < nbt * nsw; it += 32) {
+                const int n = (int)(((unsigned long long)(unsigned)it * nbt_inv) >> 24), r = it - n * nbt;
+                const int oc = (r >= nb0) + (r >= q1) + (r >= q2);
+                const int u = r - (oc == 0 ? 0 : oc == 1 ? nb0 : oc == 2 ? q1 : q2);
                 const unsigned char *ob = pr_smem + (size_t)(warp * PR_OCT + oc) * L.total;
                 const float4 *samp = reinterpret_cast<const float4 *>(ob);
                 const float4 *sdi = reinterpret_cast<const float4 *>(ob + L.stage);
