@@ -18,17 +18,21 @@ namespace mvs {
 __global__ void __launch_bounds__(256) k_project_inv(const float *__restrict__ full, float *__restrict__ proj, int W,
                                                      int H, int N, int V, int aw, float bl_ratio, int z0)
 {
+    extern __shared__ float2 pi_dv[];   // [V] camera offset (ref - view) of every view, as floats
     const int pix = blockIdx.x * blockDim.x + threadIdx.x;
     const int ref = z0 + blockIdx.y;
+    const int rx = ref % aw, ry = ref / aw;
+    for (int i = threadIdx.x; i < V; i += blockDim.x) pi_dv[i] = make_float2((float)(rx - i % aw), (float)(ry - i / aw));
+    __syncthreads();
     if (pix >= N) return;
     const int y = pix / W, x = pix - y * W;
-    const int rx = ref % aw, ry = ref / aw;
+    const float fx = (float)x, fy = (float)y;
     float m = full[(size_t)N * ref + pix];
     for (int i = 0; i < V; ++i) {
         if (i == ref) continue;
-        const int cx = i % aw, cy = i / aw;
-        const int px = f2i((float)x - round_haz(m * (float)(rx - cx)));
-        const int py = f2i((float)y - round_haz(bl_ratio * m * (float)(ry - cy)));
+        const float2 dv = pi_dv[i];
+        const int px = f2i(fx - round_haz(m * dv.x));
+        const int py = f2i(fy - round_haz(bl_ratio * m * dv.y));
         if (px >= 0 && py >= 0 && px < W && py < H) {
             const float cur = full[(size_t)N * i + (size_t)W * py + px];
             if (m < cur) m = cur;
@@ -49,13 +53,17 @@ __global__ void __launch_bounds__(RV_THREADS) k_remove_inconsistency(const float
                                                                      float *__restrict__ out, int W, int H, int N, int V,
                                                                      int aw, float bl_ratio, float fuse, int z0)
 {
-    extern __shared__ float rv_s[];   // [V][RV_THREADS]
+    extern __shared__ float rv_s[];   // [V][RV_THREADS] candidates, then [V] float2 camera offsets (view - ref)
+    float2 *rv_dv = reinterpret_cast<float2 *>(rv_s + (size_t)V * RV_THREADS);
     const int t = threadIdx.x;
     const int pix = blockIdx.x * RV_THREADS + t;
     const int ref = z0 + blockIdx.y;
+    const int rx = ref % aw, ry = ref / aw;
+    for (int i = t; i < V; i += RV_THREADS) rv_dv[i] = make_float2((float)(i % aw - rx), (float)(i / aw - ry));
+    __syncthreads();
     if (pix >= N) return;
     const int y = pix / W, x = pix - y * W;
-    const int rx = ref % aw, ry = ref / aw;
+    const float fx = (float)x, fy = (float)y;
     const int nc = ref + 1;   // slices above ref are still zero when view ref is voted
     for (int i = 0; i < nc; ++i) rv_s[i * RV_THREADS + t] = proj[(size_t)N * i + pix];
     float d_est = 0.0f;
@@ -74,10 +82,11 @@ __global__ void __launch_bounds__(RV_THREADS) k_remove_inconsistency(const float
                     if (fabsf(diff) <= fuse) stability += 1;
                 }
             }
+            const float bd = bl_ratio * d;
             for (int j = 0; j < V; ++j) {
-                const int cx = j % aw, cy = j / aw;
-                const int px = f2i((float)x - round_haz(d * (float)(cx - rx)));
-                const int py = f2i((float)y - round_haz(bl_ratio * d * (float)(cy - ry)));
+                const float2 dv = rv_dv[j];
+                const int px = f2i(fx - round_haz(d * dv.x));
+                const int py = f2i(fy - round_haz(bd * dv.y));
                 if (px >= 0 && py >= 0 && px < W && py < H) {
                     const float dc = full[(size_t)N * j + (size_t)W * py + px];
                     const float diff = dc - d;
@@ -97,12 +106,12 @@ int launch_view_fusion(const FrameDev &f, float bl_ratio, float fuse, int z0, in
 {
     if (z1 <= z0) return 0;
     if (!f.disp || !f.disp_proj || !f.disp_fused) return -1;
-    const size_t smem = sizeof(float) * (size_t)f.V * RV_THREADS;
+    const size_t smem = sizeof(float) * (size_t)f.V * RV_THREADS + sizeof(float2) * (size_t)f.V;
     if (smem > 200 * 1024) return -1;
     if (smem > 48 * 1024)
         cudaFuncSetAttribute(k_remove_inconsistency, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 g1((f.N + 255) / 256, z1);
-    k_project_inv<<<g1, 256, 0, st>>>(f.disp, f.disp_proj, f.W, f.H, f.N, f.V, f.aw, bl_ratio, 0);
+    k_project_inv<<<g1, 256, sizeof(float2) * (size_t)f.V, st>>>(f.disp, f.disp_proj, f.W, f.H, f.N, f.V, f.aw, bl_ratio, 0);
     dim3 g2((f.N + RV_THREADS - 1) / RV_THREADS, z1 - z0);
     k_remove_inconsistency<<<g2, RV_THREADS, smem, st>>>(f.disp_proj, f.disp, f.disp_fused, f.W, f.H, f.N, f.V, f.aw,
                                                          bl_ratio, fuse, z0);

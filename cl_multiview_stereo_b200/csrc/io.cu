@@ -40,12 +40,20 @@ __device__ __forceinline__ uint8_t to_u8(float x)
     return (uint8_t)(v & 255);
 }
 
+// four pixels per thread: one 128-bit load, one 32-bit store
 __global__ void __launch_bounds__(256) k_quantise_disp(const float *__restrict__ disp, uint8_t *__restrict__ out, size_t n,
-                                                       float mn, float range)
+                                                       float mn, float range, int vec)
 {
-    const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t p = 4 * ((size_t)blockIdx.x * blockDim.x + threadIdx.x);
     if (p >= n) return;
-    out[p] = to_u8(((disp[p] - mn) / range) * 255.0f);
+    if (vec && p + 4 <= n) {
+        const float4 d = *reinterpret_cast<const float4 *>(disp + p);
+        const uint32_t o = (uint32_t)to_u8(((d.x - mn) / range) * 255.0f) | ((uint32_t)to_u8(((d.y - mn) / range) * 255.0f) << 8) |
+                           ((uint32_t)to_u8(((d.z - mn) / range) * 255.0f) << 16) | ((uint32_t)to_u8(((d.w - mn) / range) * 255.0f) << 24);
+        *reinterpret_cast<uint32_t *>(out + p) = o;
+    } else {
+        for (size_t k = p; k < n && k < p + 4; ++k) out[k] = to_u8(((disp[k] - mn) / range) * 255.0f);
+    }
 }
 
 __global__ void __launch_bounds__(256) k_quantise_state(const uint32_t *__restrict__ idx, const float4 *__restrict__ plane,
@@ -80,7 +88,9 @@ int launch_quantise_disp(const FrameDev &f, const float *src, uint8_t *out_dev, 
 {
     if (z1 <= z0) return 0;
     const size_t n = (size_t)(z1 - z0) * f.N;
-    k_quantise_disp<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src + (size_t)z0 * f.N, out_dev, n, mn, range);
+    const size_t quads = (n + 3) / 4;
+    k_quantise_disp<<<(unsigned)((quads + 255) / 256), 256, 0, st>>>(src + (size_t)z0 * f.N, out_dev, n, mn, range,
+                                                                    ((size_t)z0 * f.N) % 4 == 0 ? 1 : 0);
     return 1;
 }
 
