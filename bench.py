@@ -256,6 +256,9 @@ class CpuPath:
 def run_reference(args, rank, world):
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the reference arm is one process that should use all
+    # host cores (the OpenMP runtime reads this when the oracle libraries are loaded, below)
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     cp = CpuPath(args.workload)
     cp.prepare()
     for k in range(args.warmup):
