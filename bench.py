@@ -285,7 +285,28 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "stage_ms": stages, "sample_wall_s_per_step": wall / max(args.steps, 1), "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def _stdout_to_stderr():
+    """stdout carries exactly one JSON line: libraries that write to fd 1 on their own (NCCL prints its version
+    banner there when the first communicator is created) are sent to stderr for the rest of the run"""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def workload_config(name, s, W, H):
@@ -302,6 +323,7 @@ def workload_config(name, s, W, H):
 def run_ours(args, rank, world, local_rank):
     dist = None
     if world > 1:
+        _stdout_to_stderr()
         import torch                      # plumbing only: rendezvous, barrier, max over ranks
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
@@ -470,7 +492,7 @@ def run_ours(args, rank, world, local_rank):
             "roofline": roofline, "stage_ms": stage, "stage_hbm": stage_hbm,
             "cpu_baseline": cpu, "view_sharded": view_sharded,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     frame.close()
     ctx.close()
     if dist is not None:
@@ -484,6 +506,7 @@ def run_ours(args, rank, world, local_rank):
 def run_slic_batch(args, rank, world, local_rank):
     dist = None
     if world > 1:
+        _stdout_to_stderr()
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
@@ -563,7 +586,7 @@ def run_slic_batch(args, rank, world, local_rank):
             pass
         alg = stage_bytes(W, H, s.spixl_size, s.no_iter, s.no_prop)["slic"] * B
         gbs = alg / (ms * 1e-3) / 1e9
-        print(json.dumps({
+        emit({
             "metric": "SLIC images/s", "value": world * B * 1e3 / ms, "unit": "images/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -577,7 +600,7 @@ def run_slic_batch(args, rank, world, local_rank):
             "gpu_launches": int(launches),
             "roofline": {"kernel": "slic (13 launches per batch)", "bound": "hbm", "achieved": gbs, "peak": peak,
                          "unit": "GB/s", "frac": gbs / peak, "traffic": None, "alg_bytes_per_step": alg},
-            "cpu_baseline": None}), flush=True)
+            "cpu_baseline": None})
     frame.close(); ctx.close()
     if dist is not None:
         dist.barrier()
