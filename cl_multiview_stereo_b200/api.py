@@ -237,10 +237,20 @@ class Frame:
         check(lib().mvs_frame_upload_bgr(self._h, v0, v1, _ptr(a)))
 
     def export_u8(self, which, min_disp, max_disp, element=0, v0=0, v1=None):
-        """8-bit visualisation image quantised on the device (plot_full_image / img_translate_state)"""
+        """8-bit visualisation image quantised on the device: plot_full_image (BUF_DISP, BUF_DISP_FUSED),
+        img_translate_state (BUF_STATE_A/B + element), img_translate (BUF_MAP), img_translate_flatness (BUF_FLAT)"""
         v1 = self.V if v1 is None else v1
         out = np.empty((v1 - v0, self.H, self.W), np.uint8)
         check(lib().mvs_frame_export_u8(self._h, which, int(element), int(min_disp), int(max_disp), v0, v1, _ptr(out)))
+        return out
+
+    def draw_segmentation(self, out, v0=0, v1=None):
+        """clSLIC::draw_segmentation_lines on the device; `out` uint8 [v1-v0, H, W, 4] is updated in place
+        (its one-pixel frame and pad bytes are kept, as in the reference)"""
+        v1 = self.V if v1 is None else v1
+        if out.dtype != np.uint8 or not out.flags.c_contiguous or out.size != (v1 - v0) * self.H * self.W * 4:
+            raise MvsError(f"draw_segmentation: expected contiguous uint8 {(v1 - v0, self.H, self.W, 4)}")
+        check(lib().mvs_frame_draw_segmentation(self._h, v0, v1, _ptr(out)))
         return out
 
     def dev_ptr(self, which):

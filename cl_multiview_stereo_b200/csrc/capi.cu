@@ -770,7 +770,7 @@ extern "C" int mvs_frame_run(mvs_frame *f)
 // ---- device-side ingest / export -------------------------------------
 static int need_io_stage(mvs_frame *f)
 {
-    if (!f->d.io_stage) CK(cudaMalloc(&f->d.io_stage, (size_t)f->d.V * f->d.N * 3));
+    if (!f->d.io_stage) CK(cudaMalloc(&f->d.io_stage, (size_t)f->d.V * f->d.N * 4));
     return 0;
 }
 
@@ -795,6 +795,8 @@ extern "C" int mvs_frame_upload_bgr(mvs_frame *f, int v0, int v1, const uint8_t 
 //   which = MVS_BUF_DISP / MVS_BUF_DISP_FUSED: plot_full_image (depth_refinement.cpp:1476-1497)
 //   which = MVS_BUF_STATE_A / _B with element 0 (d), 1 (smoothness), 2 (consistency):
 //           img_translate_state (depth_refinement.cpp:1500-1560)
+//   which = MVS_BUF_MAP: img_translate (photo_consistency.cpp:414-436), the block-matching disparity s7
+//   which = MVS_BUF_FLAT: img_translate_flatness (depth_refinement.cpp:299-321), ceil(flatness.s0 * 255)
 extern "C" int mvs_frame_export_u8(mvs_frame *f, int which, int element, int min_disp, int max_disp, int v0, int v1,
                                    uint8_t *host)
 {
@@ -811,11 +813,36 @@ extern "C" int mvs_frame_export_u8(mvs_frame *f, int which, int element, int min
     } else if (which == MVS_BUF_STATE_A || which == MVS_BUF_STATE_B) {
         if (element < 0 || element > 2) return fail("state element %d: only 0 (d), 1 (smoothness), 2 (consistency)", element);
         f->ctx->launches += launch_quantise_state(f->d, which == MVS_BUF_STATE_B, element, f->d.io_stage, mn, range, v0, v1, st);
+    } else if (which == MVS_BUF_MAP || which == MVS_BUF_FLAT) {
+        if (!f->d.idx || !f->d.map) return fail("frame has no label / superpixel buffers");
+        if (which == MVS_BUF_FLAT && !f->d.flat) return fail("frame has no flatness buffer");
+        f->ctx->launches += which == MVS_BUF_MAP
+                                ? launch_quantise_spixl(f->d, (const float *)f->d.map, 8, 7, 0, f->d.io_stage, mn, range, v0, v1, st)
+                                : launch_quantise_spixl(f->d, (const float *)f->d.flat, 2, 0, 1, f->d.io_stage, mn, range, v0, v1, st);
     } else {
         return fail("mvs_frame_export_u8: buffer %d has no 8-bit image form", which);
     }
     if (check_launch("export_u8")) return 1;
     CK(cudaMemcpyAsync(host, f->d.io_stage, (size_t)(v1 - v0) * f->d.N, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// clSLIC::draw_segmentation_lines (clSLIC.cpp:447-478) for views [v0, v1) from the frame's resident image and
+// labels.  `rgbx` is in/out like the reference's out_img: its one-pixel frame and pad bytes come back unchanged.
+extern "C" int mvs_frame_draw_segmentation(mvs_frame *f, int v0, int v1, uint8_t *rgbx)
+{
+    if (!f || !rgbx) return fail("null argument");
+    if (!f->d.rgbx || !f->d.idx) return fail("frame has no image / label buffers");
+    if (v0 < 0 || v1 > f->d.V || v0 > v1) return fail("bad view range [%d,%d)", v0, v1);
+    CK(cudaSetDevice(f->ctx->device));
+    if (need_io_stage(f)) return 1;
+    cudaStream_t st = f->ctx->stream;
+    const size_t bytes = (size_t)(v1 - v0) * f->d.N * 4;
+    CK(cudaMemcpyAsync(f->d.io_stage, rgbx, bytes, cudaMemcpyHostToDevice, st));
+    f->ctx->launches += launch_segmentation_lines(f->d, (uchar4 *)f->d.io_stage, v0, v1, st);
+    if (check_launch("draw_segmentation")) return 1;
+    CK(cudaMemcpyAsync(rgbx, f->d.io_stage, bytes, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     return 0;
 }

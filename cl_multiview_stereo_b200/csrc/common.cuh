@@ -23,7 +23,7 @@ struct FrameDev {
     float *disp;        // [V][N]
     float *disp_proj;   // [V][N]   multi-view fusion: chased disparity (allocated on demand)
     float *disp_fused;  // [V][N]   multi-view fusion: voted disparity (allocated on demand)
-    uint8_t *io_stage;  // [V][N][3] staging of packed BGR input / 8-bit output (allocated on demand)
+    uint8_t *io_stage;  // [V][N][4] staging of packed BGR input / 8-bit and overlay output (allocated on demand)
     int *view_subset;   // [V][V]
     int *subset_num;    // [V]
     float *levels;      // [L]
@@ -64,6 +64,9 @@ int launch_quantise_disp(const FrameDev &f, const float *src, uint8_t *out_dev, 
                          cudaStream_t st);
 int launch_quantise_state(const FrameDev &f, int which, int element, uint8_t *out_dev, float mn, float range, int z0,
                           int z1, cudaStream_t st);
+int launch_quantise_spixl(const FrameDev &f, const float *src, int stride, int off, int mode, uint8_t *out_dev, float mn,
+                          float range, int z0, int z1, cudaStream_t st);
+int launch_segmentation_lines(const FrameDev &f, uchar4 *out_dev, int z0, int z1, cudaStream_t st);
 int launch_export_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
 int launch_import_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
 

@@ -6,6 +6,12 @@
 //                     (unsigned char)floor((d - min) / (max - min) * 255)
 //   k_quantise_state  img_translate_state (depth_refinement.cpp:1500-1560): per-pixel image of one state
 //                     element of the pixel's superpixel, elements 0 (d), 1 (smoothness), 2 (consistency)
+//   k_quantise_spixl  img_translate (photo_consistency.cpp:414-436): the block-matching disparity s7 of the
+//                     pixel's superpixel, floor-quantised like plot_full_image; img_translate_flatness
+//                     (depth_refinement.cpp:299-321): (unsigned char)ceil(flatness.s0 * 255)
+//   k_segmentation_lines  clSLIC::draw_segmentation_lines (clSLIC.cpp:447-478): interior pixels whose
+//                     4-neighbourhood holds another label become {0,0,255}, the others take the input
+//                     colour; the one-pixel frame and the pad byte of the output are never written
 #include "common.cuh"
 #include "mvs_math.cuh"
 
@@ -71,6 +77,38 @@ __global__ void __launch_bounds__(256) k_quantise_state(const uint32_t *__restri
     out[(size_t)blockIdx.y * N + p] = to_u8(v);
 }
 
+// per-pixel image of one float of the pixel's superpixel record (`stride` floats per superpixel, element
+// `off`).  mode 0: floor(((v - mn) / range) * 255); mode 1: ceil(v * 255)
+__global__ void __launch_bounds__(256) k_quantise_spixl(const uint32_t *__restrict__ idx, const float *__restrict__ src,
+                                                        uint8_t *__restrict__ out, int N, int M, int stride, int off,
+                                                        int mode, float mn, float range, int z0)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int z = z0 + blockIdx.y;
+    if (p >= N) return;
+    const float v = src[((size_t)z * M + idx[(size_t)z * N + p]) * stride + off];
+    // to_u8 floors an already integral value in mode 1; it pins the out-of-range cast for both modes
+    out[(size_t)blockIdx.y * N + p] = mode == 0 ? to_u8(((v - mn) / range) * 255.0f) : to_u8(ceilf(v * 255.0f));
+}
+
+// one thread per pixel of the interior; `out` is read-modify-written so that its pad byte survives
+__global__ void __launch_bounds__(256) k_segmentation_lines(const uint32_t *__restrict__ idx, const uchar4 *__restrict__ in,
+                                                            uchar4 *__restrict__ out, int W, int H, int z0)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x < 1 || x >= W - 1 || y < 1 || y >= H - 1) return;
+    const size_t N = (size_t)W * H;
+    const size_t p = (size_t)(z0 + blockIdx.z) * N + (size_t)y * W + x;
+    const size_t q = (size_t)blockIdx.z * N + (size_t)y * W + x;
+    const uint32_t l = idx[p];
+    const bool edge = l != idx[p + 1] || l != idx[p - 1] || l != idx[p - W] || l != idx[p + W];
+    uchar4 o = out[q];
+    if (edge) { o.x = 0; o.y = 0; o.z = 255; }
+    else { const uchar4 c = in[p]; o.x = c.x; o.y = c.y; o.z = c.z; }
+    out[q] = o;
+}
+
 int launch_ingest_bgr(const FrameDev &f, const void *bgr_dev, int z0, int z1, cudaStream_t st)
 {
     if (z1 <= z0) return 0;
@@ -100,6 +138,23 @@ int launch_quantise_state(const FrameDev &f, int which, int element, uint8_t *ou
     if (z1 <= z0) return 0;
     dim3 g((f.N + 255) / 256, z1 - z0);
     k_quantise_state<<<g, 256, 0, st>>>(f.idx, f.plane[which], f.cost[which], out_dev, f.N, f.M, element, mn, range, z0);
+    return 1;
+}
+
+int launch_quantise_spixl(const FrameDev &f, const float *src, int stride, int off, int mode, uint8_t *out_dev, float mn,
+                          float range, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    dim3 g((f.N + 255) / 256, z1 - z0);
+    k_quantise_spixl<<<g, 256, 0, st>>>(f.idx, src, out_dev, f.N, f.M, stride, off, mode, mn, range, z0);
+    return 1;
+}
+
+int launch_segmentation_lines(const FrameDev &f, uchar4 *out_dev, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0 || f.W < 3 || f.H < 3) return 0;
+    dim3 g((f.W + 255) / 256, f.H, z1 - z0);
+    k_segmentation_lines<<<g, 256, 0, st>>>(f.idx, f.rgbx, out_dev, f.W, f.H, z0);
     return 1;
 }
 

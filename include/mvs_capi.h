@@ -108,9 +108,15 @@ int mvs_frame_dev_ptr(mvs_frame *f, int which, void **dev);
 int mvs_frame_upload_bgr(mvs_frame *f, int v0, int v1, const uint8_t *bgr);
 /* 8-bit visualisation images quantised on the device: plot_full_image (depth_refinement.cpp:1476-1497) for
  * MVS_BUF_DISP / MVS_BUF_DISP_FUSED; img_translate_state (depth_refinement.cpp:1500-1560) for MVS_BUF_STATE_A/B
- * with element 0 (d), 1 (smoothness), 2 (consistency).  host: uint8[(v1-v0)*H*W] */
+ * with element 0 (d), 1 (smoothness), 2 (consistency); img_translate (photo_consistency.cpp:414-436) for
+ * MVS_BUF_MAP (block-matching disparity s7); img_translate_flatness (depth_refinement.cpp:299-321) for
+ * MVS_BUF_FLAT (ceil(flatness.s0 * 255), min/max unused).  host: uint8[(v1-v0)*H*W] */
 int mvs_frame_export_u8(mvs_frame *f, int which, int element, int min_disp, int max_disp, int v0, int v1,
                         uint8_t *host);
+/* clSLIC::draw_segmentation_lines (clSLIC.h:20, clSLIC.cpp:447-478) from the resident image and labels of views
+ * [v0,v1): interior pixels next to another label become {0,0,255}, the others take the input colour.  rgbx
+ * (uint8[(v1-v0)*H*W*4]) is in/out like the reference's out_img: its one-pixel frame and pad bytes are kept. */
+int mvs_frame_draw_segmentation(mvs_frame *f, int v0, int v1, uint8_t *rgbx);
 int mvs_frame_sizes(mvs_frame *f, int *V, int *W, int *H, int *mw, int *mh, int *num_levels);
 
 /* clSLIC::do_super_pixel_seg (clSLIC.cpp:67-122) for the frame's own views, all views per launch */

@@ -996,6 +996,47 @@ void orc_img_translate_state(const float *state, const uint32_t *idx, uint8_t *o
         }
 }
 
+/* clPhotoConsistency::img_translate (photo_consistency.cpp:414-436): the block-matching disparity
+ * (spixl_map .s7) of each pixel's superpixel, floor-quantised.  map: float[V][M][8] */
+void orc_img_translate(const float *map, const uint32_t *idx, uint8_t *out, int V, int W, int H, int mw, int mh,
+                       float min_disp, float max_disp)
+{
+    size_t N = (size_t)W * H, M = (size_t)mw * mh;
+    for (int k = 0; k < V; ++k)
+        for (size_t p = 0; p < N; ++p) {
+            float d = map[8 * (M * k + idx[N * k + p]) + 7];
+            out[N * k + p] = o_to_u8(((d - min_disp) / (max_disp - min_disp)) * 255);
+        }
+}
+
+/* clDepthRefinement::img_translate_flatness (depth_refinement.cpp:299-321): (unsigned char)ceil(fl.s0 * 255).
+ * flat: float[V][M][2] */
+void orc_img_translate_flatness(const float *flat, const uint32_t *idx, uint8_t *out, int V, int W, int H, int mw, int mh)
+{
+    size_t N = (size_t)W * H, M = (size_t)mw * mh;
+    for (int k = 0; k < V; ++k)
+        for (size_t p = 0; p < N; ++p) {
+            float d = flat[2 * (M * k + idx[N * k + p])];
+            out[N * k + p] = o_to_u8(ceilf(d * 255));
+        }
+}
+
+/* clSLIC::draw_segmentation_lines (clSLIC.cpp:447-478), one image.  in/out: uchar[H][W][4]; only bytes 0..2 of
+ * interior pixels are written */
+void orc_draw_segmentation_lines(const uint32_t *idx, const uint8_t *in, uint8_t *out, int W, int H)
+{
+    for (int i = 1; i < H - 1; i++)
+        for (int j = 1; j < W - 1; j++) {
+            size_t p = (size_t)i * W + j;
+            uint32_t l = idx[p];
+            if (l != idx[p + 1] || l != idx[p - 1] || l != idx[p - W] || l != idx[p + W]) {
+                out[4 * p] = 0; out[4 * p + 1] = 0; out[4 * p + 2] = 255;
+            } else {
+                out[4 * p] = in[4 * p]; out[4 * p + 1] = in[4 * p + 1]; out[4 * p + 2] = in[4 * p + 2];
+            }
+        }
+}
+
 /* ------------------------------------------------------------------------ */
 /* vector wrappers of the pinned math (tests compare them with libm and with
  * the CUDA copy in csrc/mvs_math.cuh)                                       */

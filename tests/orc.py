@@ -228,6 +228,28 @@ class Oracle:
                                          int(element), int(min_disp), int(max_disp))
         return out
 
+    def img_translate(self, mp, idx, min_disp, max_disp):
+        V, H, W = idx.shape
+        mh, mw = mp.shape[1:3]
+        out = np.zeros((V, H, W), u8)
+        self.lib.orc_img_translate(_p(np.ascontiguousarray(mp, f32)), _p(idx), _p(out), V, W, H, mw, mh,
+                                   C.c_float(min_disp), C.c_float(max_disp))
+        return out
+
+    def img_translate_flatness(self, flat, idx):
+        V, H, W = idx.shape
+        mh, mw = flat.shape[1:3]
+        out = np.zeros((V, H, W), u8)
+        self.lib.orc_img_translate_flatness(_p(np.ascontiguousarray(flat, f32)), _p(idx), _p(out), V, W, H, mw, mh)
+        return out
+
+    def draw_segmentation_lines(self, idx, img, out):
+        """idx [H,W] u32, img / out [H,W,4] u8; out is updated in place and returned"""
+        H, W = idx.shape
+        self.lib.orc_draw_segmentation_lines(_p(np.ascontiguousarray(idx, np.uint32)), _p(np.ascontiguousarray(img, u8)),
+                                             _p(out), W, H)
+        return out
+
     # ---- whole pipeline (pipeline::exe_pipeline with perform_depth_est enabled)
     def pipeline(self, rgbx, s):
         """rgbx [V,H,W,4]; s = SystemSettings-like.  Returns dict of every stage output."""

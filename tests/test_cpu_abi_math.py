@@ -134,3 +134,34 @@ def test_host_byte_work_restatement(oracle):
     assert np.array_equal(oracle.plot_full_image(d, 30, 60), want)
     hostile = np.array([np.nan, np.inf, -np.inf, 1e20, -1.0, 61.0], np.float32)
     assert list(oracle.plot_full_image(hostile, 30, 60)) == [0, 0, 0, 0, (-264) & 255, 263 & 255]
+
+
+def test_visualisation_restatements(oracle):
+    """img_translate, img_translate_flatness and draw_segmentation_lines restated in oracle.c against plain numpy
+    (photo_consistency.cpp:414-436, depth_refinement.cpp:299-321, clSLIC.cpp:447-478)"""
+    rng = np.random.default_rng(11)
+    V, H, W, mh, mw = 2, 9, 11, 3, 4
+    idx = rng.integers(0, mh * mw, size=(V, H, W), dtype=np.uint32)
+    mp = rng.uniform(30, 60, size=(V, mh, mw, 8)).astype(np.float32)
+    flat = rng.uniform(0, 1, size=(V, mh, mw, 2)).astype(np.float32)
+    flat[0, 0, 0, 0], flat[0, 0, 1, 0] = 1.0, 0.0
+    d = np.stack([mp[v].reshape(-1, 8)[idx[v], 7] for v in range(V)])
+    want = np.floor((d - np.float32(30)) / np.float32(30) * np.float32(255)).astype(np.uint8)
+    assert np.array_equal(oracle.img_translate(mp, idx, 30, 60), want)
+    fl = np.stack([flat[v].reshape(-1, 2)[idx[v], 0] for v in range(V)])
+    want = np.ceil(fl * np.float32(255)).astype(np.int32).astype(np.uint8)
+    assert np.array_equal(oracle.img_translate_flatness(flat, idx), want)
+    # overlay: the frame and the pad byte of `out` are never written
+    lab = (np.arange(H)[:, None] // 4 * 3 + np.arange(W)[None, :] // 4).astype(np.uint32)
+    img = rng.integers(0, 256, size=(H, W, 4), dtype=np.uint8)
+    out0 = rng.integers(0, 256, size=(H, W, 4), dtype=np.uint8)
+    out = oracle.draw_segmentation_lines(lab, img, out0.copy())
+    edge = np.zeros((H, W), bool)
+    c = lab[1:-1, 1:-1]
+    edge[1:-1, 1:-1] = (c != lab[1:-1, 2:]) | (c != lab[1:-1, :-2]) | (c != lab[:-2, 1:-1]) | (c != lab[2:, 1:-1])
+    want = out0.copy()
+    want[1:-1, 1:-1, :3] = img[1:-1, 1:-1, :3]
+    want[edge, :3] = (0, 0, 255)
+    assert np.array_equal(out, want) and edge.any() and not edge.all()
+    tiny = out0[:2, :2].copy()
+    assert np.array_equal(oracle.draw_segmentation_lines(lab[:2, :2], img[:2, :2].copy(), tiny.copy()), tiny)

@@ -381,6 +381,52 @@ def test_export_u8_matches_reference_quantisation(ctx, oracle, small_frame):
         f.close()
 
 
+def test_export_of_superpixel_images_and_overlay(ctx, oracle, small_frame):
+    """img_translate (photo_consistency.cpp:414-436), img_translate_flatness (depth_refinement.cpp:299-321) and
+    clSLIC::draw_segmentation_lines (clSLIC.cpp:447-478) from the resident frame"""
+    s, rgbx, gt, ref = small_frame
+    f = mvs.Frame(ctx, s, 192, 128)
+    try:
+        f.upload(mvs.BUF_RGBX, rgbx)
+        f.run()
+        idx, mp, flat = f.download(mvs.BUF_IDX), f.download(mvs.BUF_MAP), f.download(mvs.BUF_FLAT)
+        mp[0, 0, :6, 7] = [np.nan, np.inf, -1e20, -3.5, 300.0, 15.999]
+        f.upload(mvs.BUF_MAP, mp)
+        for lo, hi in ((s.min_disp, s.max_disp), (3, 11)):
+            assert np.array_equal(f.export_u8(mvs.BUF_MAP, lo, hi), oracle.img_translate(mp, idx, lo, hi))
+        assert np.array_equal(f.export_u8(mvs.BUF_MAP, 0, 16, v0=1, v1=4), oracle.img_translate(mp[1:4], idx[1:4], 0, 16))
+        flat[0, 0, :5, 0] = [np.nan, 0.0, 1.0, 2.5, -0.25]
+        f.upload(mvs.BUF_FLAT, flat)
+        assert np.array_equal(f.export_u8(mvs.BUF_FLAT, 0, 1), oracle.img_translate_flatness(flat, idx))
+        rng = np.random.default_rng(3)
+        out0 = rng.integers(0, 256, size=rgbx.shape, dtype=np.uint8)
+        want = np.stack([oracle.draw_segmentation_lines(idx[v], rgbx[v], out0[v].copy()) for v in range(len(idx))])
+        assert np.array_equal(f.draw_segmentation(out0.copy()), want)
+        assert (want[..., :3] != out0[..., :3]).any()
+        assert np.array_equal(f.draw_segmentation(out0[2:5].copy(), 2, 5), want[2:5])
+        with pytest.raises(mvs.MvsError):
+            f.draw_segmentation(np.zeros((1, 4, 4, 4), np.uint8))
+    finally:
+        f.close()
+
+
+@pytest.mark.parametrize("W,H", [(37, 29), (8, 8), (17, 9)])
+def test_overlay_ragged_and_degenerate_sizes(ctx, oracle, W, H):
+    s = small_settings(2, 1)
+    rng = np.random.default_rng(W * 7 + H)
+    rgbx = rng.integers(0, 256, size=(2, H, W, 4), dtype=np.uint8)
+    f = mvs.Frame(ctx, s, W, H)
+    try:
+        f.upload(mvs.BUF_RGBX, rgbx)
+        f.slic()
+        idx = f.download(mvs.BUF_IDX)
+        out0 = rng.integers(0, 256, size=rgbx.shape, dtype=np.uint8)
+        want = np.stack([oracle.draw_segmentation_lines(idx[v], rgbx[v], out0[v].copy()) for v in range(2)])
+        assert np.array_equal(f.draw_segmentation(out0.copy()), want)
+    finally:
+        f.close()
+
+
 def test_refinement_with_far_labels(ctx, oracle, small_frame):
     """hand-made label map: 1 % of the pixels carry the label of an arbitrary, far-away superpixel (SLIC never
     produces that); the consistency gathers must follow the label wherever it points"""
