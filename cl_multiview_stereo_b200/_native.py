@@ -34,7 +34,7 @@ SYMBOLS = [
     "mvs_frame_init_state", "mvs_frame_propagate", "mvs_frame_fusion", "mvs_frame_run", "mvs_frame_exchange",
     "mvs_frame_stage_ms", "mvs_frame_set_timing", "mvs_slic_run", "mvs_bm_run", "mvs_refine_run",
     "mvs_frame_view_fusion", "mvs_view_fusion_run", "mvs_frame_upload_bgr", "mvs_frame_export_u8",
-    "mvs_frame_draw_segmentation",
+    "mvs_frame_draw_segmentation", "mvs_view_partition_weighted", "mvs_exchange_plan_for", "mvs_frame_set_partition",
 ]
 
 _lib = None

@@ -139,14 +139,41 @@ def view_partition(V, nranks, rank):
     return lo.value, hi.value
 
 
-def exchange_plan(V, nranks, subset, subset_num):
-    """the halo transfers mvs_frame_exchange issues: list of (view, source rank, destination rank)"""
+def view_partition_weighted(weights, nranks):
+    """contiguous view ranges [(lo, hi)] * nranks that minimise the heaviest rank's summed weight"""
+    w = np.ascontiguousarray(weights, np.int32)
+    out = np.zeros((int(nranks), 2), np.int32)
+    check(lib().mvs_view_partition_weighted(len(w), int(nranks), _ptr(w), _ptr(out)))
+    return [(int(a), int(b)) for a, b in out]
+
+
+def view_weights(subset_num, base=33, per_neighbour=10):
+    """work of a view relative to the others: a constant part (SLIC, boundary, fusion, the smoothness and bookkeeping
+    share of propagate) plus a part per neighbour view (block matching, state initialisation, the consistency share of
+    propagate).  33 : 10 is the split measured on the 15-view 1080p frame"""
+    return [int(base + per_neighbour * int(k)) for k in subset_num]
+
+
+def exchange_plan(V, nranks, subset, subset_num, parts=None):
+    """the halo transfers mvs_frame_exchange issues: list of (view, source rank, destination rank); parts = the
+    view ranges of all ranks when they are not view_partition's"""
     subset = np.ascontiguousarray(subset, np.int32)
     subset_num = np.ascontiguousarray(subset_num, np.int32)
     n = C.c_int()
-    check(lib().mvs_exchange_plan(int(V), int(nranks), _ptr(subset), _ptr(subset_num), None, 0, C.byref(n)))
+    if parts is None:
+        def call(t, cap):
+            return lib().mvs_exchange_plan(int(V), int(nranks), _ptr(subset), _ptr(subset_num), t, cap, C.byref(n))
+    else:
+        table = np.ascontiguousarray(parts, np.int32).reshape(-1)
+        if table.size != 2 * int(nranks):
+            raise MvsError(f"exchange_plan: {table.size // 2} view ranges for {nranks} ranks")
+
+        def call(t, cap):
+            return lib().mvs_exchange_plan_for(int(V), int(nranks), _ptr(table), _ptr(subset), _ptr(subset_num), t, cap,
+                                               C.byref(n))
+    check(call(None, 0))
     t = np.zeros((max(n.value, 1), 3), np.int32)
-    check(lib().mvs_exchange_plan(int(V), int(nranks), _ptr(subset), _ptr(subset_num), _ptr(t), n.value, C.byref(n)))
+    check(call(_ptr(t), n.value))
     return [tuple(int(x) for x in row) for row in t[:n.value]]
 
 
@@ -243,6 +270,11 @@ class Frame:
         out = np.empty((v1 - v0, self.H, self.W), np.uint8)
         check(lib().mvs_frame_export_u8(self._h, which, int(element), int(min_disp), int(max_disp), v0, v1, _ptr(out)))
         return out
+
+    def set_partition(self, parts):
+        """view ranges [(lo, hi)] of ALL ranks when they are not view_partition's (same table on every rank)"""
+        table = np.ascontiguousarray(parts, np.int32).reshape(-1)
+        check(lib().mvs_frame_set_partition(self._h, table.size // 2, _ptr(table)))
 
     def draw_segmentation(self, out, v0=0, v1=None):
         """clSLIC::draw_segmentation_lines on the device; `out` uint8 [v1-v0, H, W, 4] is updated in place

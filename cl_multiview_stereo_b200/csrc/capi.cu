@@ -99,6 +99,7 @@ struct mvs_frame {
     mvs_params p{};
     FrameDev d{};
     int lo = 0, hi = 0;
+    std::vector<int> part;         // {lo, hi} of every rank (mvs_frame_set_partition); empty = mvs_view_partition
     std::vector<int> h_subset, h_subset_num;
     std::vector<float> h_levels;
     // refinement scalars (set by prepare_refine)
@@ -228,6 +229,42 @@ extern "C" int mvs_view_partition(int V, int nranks, int rank, int *lo, int *hi)
     int l = rank * base + std::min(rank, rem);
     *lo = l;
     *hi = l + base + (rank < rem ? 1 : 0);
+    return 0;
+}
+
+// Contiguous partition of V weighted views over n ranks that minimises the heaviest rank; among those, the one
+// with the smallest sum of squared rank weights (so no rank is left empty while another holds two views).
+// A view's work grows with its number of neighbour views (3 at a corner of the camera grid, 8 inside), so equal
+// view counts leave the ranks that own the interior views with up to twice the work of the others.
+// lo_hi: 2*nranks ints {lo_0, hi_0, lo_1, hi_1, ...}.  Pure host code, the same table on every rank.
+extern "C" int mvs_view_partition_weighted(int V, int nranks, const int *weight, int *lo_hi)
+{
+    if (V < 0 || nranks <= 0 || !lo_hi || (V > 0 && !weight)) return fail("mvs_view_partition_weighted: bad argument");
+    std::vector<long long> pre(V + 1, 0);
+    for (int v = 0; v < V; ++v) {
+        if (weight[v] <= 0) return fail("weight[%d] = %d must be positive", v, weight[v]);
+        pre[v + 1] = pre[v] + weight[v];
+    }
+    struct Cost { long long mx; double sq; };
+    auto better = [](const Cost &a, const Cost &b) { return a.mx < b.mx || (a.mx == b.mx && a.sq < b.sq); };
+    const Cost none{-1, 0.0};
+    // best[k][i]: the first i views over the first k ranks
+    std::vector<std::vector<Cost>> best(nranks + 1, std::vector<Cost>(V + 1, none));
+    std::vector<std::vector<int>> cut(nranks + 1, std::vector<int>(V + 1, 0));
+    best[0][0] = Cost{0, 0.0};
+    for (int k = 1; k <= nranks; ++k)
+        for (int i = 0; i <= V; ++i)
+            for (int j = 0; j <= i; ++j) {
+                if (best[k - 1][j].mx < 0) continue;
+                const long long w = pre[i] - pre[j];
+                const Cost c{std::max(best[k - 1][j].mx, w), best[k - 1][j].sq + (double)w * (double)w};
+                if (best[k][i].mx < 0 || better(c, best[k][i])) { best[k][i] = c; cut[k][i] = j; }
+            }
+    for (int k = nranks, i = V; k >= 1; --k) {
+        lo_hi[2 * (k - 1)] = cut[k][i];
+        lo_hi[2 * (k - 1) + 1] = i;
+        i = cut[k][i];
+    }
     return 0;
 }
 
@@ -517,11 +554,13 @@ static int check_launch(const char *what)
 // rank derives the same global plan; transfers are grouped ncclSend/ncclRecv over NVLink.
 // The plan is a pure host function of (V, nranks, neighbour lists) so that it can be tested
 // without a GPU: transfers (view, src rank, dst rank) in issue order.
-static void build_exchange_plan(int V, int n, const int *subset, const int *subset_num, std::vector<int> &triples)
+static void build_exchange_plan(int V, int n, const int *part, const int *subset, const int *subset_num,
+                                std::vector<int> &triples)
 {
     std::vector<int> lo(n), hi(n), owner(V);
     for (int r = 0; r < n; ++r) {
-        mvs_view_partition(V, n, r, &lo[r], &hi[r]);
+        if (part) { lo[r] = part[2 * r]; hi[r] = part[2 * r + 1]; }
+        else mvs_view_partition(V, n, r, &lo[r], &hi[r]);
         for (int v = lo[r]; v < hi[r]; ++v) owner[v] = r;
     }
     for (int r = 0; r < n; ++r) {
@@ -533,8 +572,36 @@ static void build_exchange_plan(int V, int n, const int *subset, const int *subs
     }
 }
 
+static int check_partition(int V, int nranks, const int *lo_hi)
+{
+    int at = 0;
+    for (int r = 0; r < nranks; ++r) {
+        if (lo_hi[2 * r] != at || lo_hi[2 * r + 1] < at) return fail("partition: rank %d holds [%d,%d), expected to start at %d", r, lo_hi[2 * r], lo_hi[2 * r + 1], at);
+        at = lo_hi[2 * r + 1];
+    }
+    if (at != V) return fail("partition covers %d of %d views", at, V);
+    return 0;
+}
+
+static int exchange_plan(int V, int nranks, const int *part, const int *view_subset, const int *subset_num, int *triples,
+                         int cap, int *count);
+
 extern "C" int mvs_exchange_plan(int V, int nranks, const int *view_subset, const int *subset_num, int *triples, int cap,
                                  int *count)
+{
+    return exchange_plan(V, nranks, nullptr, view_subset, subset_num, triples, cap, count);
+}
+
+extern "C" int mvs_exchange_plan_for(int V, int nranks, const int *lo_hi, const int *view_subset, const int *subset_num,
+                                     int *triples, int cap, int *count)
+{
+    if (!lo_hi || nranks <= 0) return fail("mvs_exchange_plan_for: bad argument");
+    if (check_partition(V, nranks, lo_hi)) return 1;
+    return exchange_plan(V, nranks, lo_hi, view_subset, subset_num, triples, cap, count);
+}
+
+static int exchange_plan(int V, int nranks, const int *part, const int *view_subset, const int *subset_num, int *triples,
+                         int cap, int *count)
 {
     if (V <= 0 || nranks <= 0 || !view_subset || !subset_num || !count) return fail("mvs_exchange_plan: bad argument");
     for (int z = 0; z < V; ++z) {
@@ -543,7 +610,7 @@ extern "C" int mvs_exchange_plan(int V, int nranks, const int *view_subset, cons
             if (view_subset[z * V + k] < 0 || view_subset[z * V + k] >= V) return fail("view_subset[%d][%d] out of range", z, k);
     }
     std::vector<int> t;
-    build_exchange_plan(V, nranks, view_subset, subset_num, t);
+    build_exchange_plan(V, nranks, part, view_subset, subset_num, t);
     *count = (int)t.size() / 3;
     if (triples) {
         if (cap < *count) return fail("mvs_exchange_plan: %d transfers, room for %d", *count, cap);
@@ -557,7 +624,8 @@ static int exchange_raw(mvs_frame *f, char *base, size_t per_view)
     mvs_ctx *c = f->ctx;
     if (!c->comm || c->nranks == 1) return 0;
     std::vector<int> t;
-    build_exchange_plan(f->d.V, c->nranks, f->h_subset.data(), f->h_subset_num.data(), t);
+    build_exchange_plan(f->d.V, c->nranks, f->part.empty() ? nullptr : f->part.data(), f->h_subset.data(),
+                        f->h_subset_num.data(), t);
     NK(GroupStart());
     for (size_t i = 0; i + 2 < t.size(); i += 3) {
         const int v = t[i], src = t[i + 1], dst = t[i + 2];
@@ -577,6 +645,22 @@ static void halo_views(mvs_frame *f, std::vector<int> &out)
         for (int k = 0; k < f->h_subset_num[u]; ++k) need[f->h_subset[(size_t)u * V + k]] = 1;
     for (int v = 0; v < V; ++v)
         if (need[v] && (v < f->lo || v >= f->hi)) out.push_back(v);
+}
+
+// The view ranges of ALL ranks when they are not mvs_view_partition's (e.g. mvs_view_partition_weighted): every
+// rank passes the same table; this rank's entry must be the range the frame was created with.
+extern "C" int mvs_frame_set_partition(mvs_frame *f, int nranks, const int *lo_hi)
+{
+    if (!f || !lo_hi) return fail("null argument");
+    mvs_ctx *c = f->ctx;
+    const int n = c->comm ? c->nranks : nranks, rank = c->comm ? c->rank : -1;
+    if (nranks != n) return fail("partition for %d ranks, communicator has %d", nranks, n);
+    if (check_partition(f->d.V, nranks, lo_hi)) return 1;
+    if (rank >= 0 && (lo_hi[2 * rank] != f->lo || lo_hi[2 * rank + 1] != f->hi))
+        return fail("partition gives rank %d views [%d,%d), the frame was created for [%d,%d)", rank, lo_hi[2 * rank],
+                    lo_hi[2 * rank + 1], f->lo, f->hi);
+    f->part.assign(lo_hi, lo_hi + 2 * nranks);
+    return 0;
 }
 
 extern "C" int mvs_frame_exchange(mvs_frame *f, int which)
@@ -727,7 +811,10 @@ extern "C" int mvs_frame_view_fusion(mvs_frame *f)
     if (c->comm && c->nranks > 1 && (f->lo != 0 || f->hi != d.V)) {
         StageTimer t(f, ST_EXCH);
         std::vector<int> lo(c->nranks), hi(c->nranks);
-        for (int r = 0; r < c->nranks; ++r) mvs_view_partition(d.V, c->nranks, r, &lo[r], &hi[r]);
+        for (int r = 0; r < c->nranks; ++r) {
+            if (f->part.empty()) mvs_view_partition(d.V, c->nranks, r, &lo[r], &hi[r]);
+            else { lo[r] = f->part[2 * r]; hi[r] = f->part[2 * r + 1]; }
+        }
         const size_t per_view = sizeof(float) * (size_t)d.N;
         NK(GroupStart());
         for (int r = 0; r < c->nranks; ++r) {

@@ -85,17 +85,27 @@ int mvs_comm_unique_id(void *id128);
 int mvs_comm_init(mvs_ctx *ctx, const void *id128, int nranks, int rank);
 /* contiguous partition of V views over nranks (the plan mvs_frame_exchange assumes) */
 int mvs_view_partition(int V, int nranks, int rank, int *lo, int *hi);
+/* contiguous partition that balances per-view WEIGHTS instead of view counts (a view's work grows with its number
+ * of neighbour views: pipeline.cpp:121-142 gives a corner view 3 and an interior view 8): minimises the heaviest
+ * rank.  lo_hi: 2*nranks ints {lo_0,hi_0,lo_1,hi_1,...}.  Hand the table to mvs_frame_set_partition on every rank. */
+int mvs_view_partition_weighted(int V, int nranks, const int *weight, int *lo_hi);
 /* the halo plan mvs_frame_exchange follows (pure host code, no device needed): every transfer
  * {view, source rank, destination rank} in issue order, for the neighbour lists the reference
  * builds at pipeline.cpp:121-142.  triples may be NULL to query *count only. */
 int mvs_exchange_plan(int V, int nranks, const int *view_subset, const int *subset_num, int *triples, int cap,
                       int *count);
+/* the same for an explicit table of view ranges (mvs_view_partition_weighted) */
+int mvs_exchange_plan_for(int V, int nranks, const int *lo_hi, const int *view_subset, const int *subset_num,
+                          int *triples, int cap, int *count);
 
 /* ---- frame: device-resident pipeline over V = array_width*array_height views ---- */
 /* view_lo..view_hi-1 are the views this context computes (all views for single GPU);
  * buffers for every view are allocated because neighbour views are read (clcode.cl:1046,1314,1581). */
 int mvs_frame_create(mvs_ctx *ctx, const mvs_params *p, int view_lo, int view_hi, mvs_frame **out);
 int mvs_frame_destroy(mvs_frame *f);
+/* view ranges of all ranks when they are not mvs_view_partition's: same table on every rank, this rank's entry
+ * must be the [view_lo,view_hi) the frame was created with.  Pure host call. */
+int mvs_frame_set_partition(mvs_frame *f, int nranks, const int *lo_hi);
 /* host <-> device copy of one buffer for views [v0,v1) */
 int mvs_frame_upload(mvs_frame *f, int which, int v0, int v1, const void *host);
 int mvs_frame_download(mvs_frame *f, int which, int v0, int v1, void *host);

@@ -165,3 +165,32 @@ def test_visualisation_restatements(oracle):
     assert np.array_equal(out, want) and edge.any() and not edge.all()
     tiny = out0[:2, :2].copy()
     assert np.array_equal(oracle.draw_segmentation_lines(lab[:2, :2], img[:2, :2].copy(), tiny.copy()), tiny)
+
+
+def test_weighted_view_partition_minimises_the_heaviest_rank():
+    """mvs_view_partition_weighted against brute force over every contiguous split"""
+    import itertools
+    rng = np.random.default_rng(2)
+    cases = [(mvs.view_weights(mvs.make_subsets(5, 3)[1], b, p), n) for n in (1, 2, 4, 8) for b, p in ((33, 10), (5, 6))]
+    cases += [(list(rng.integers(1, 60, size=V)), n) for V in (1, 3, 7, 10) for n in (1, 2, 3, 5)]
+    for w, n in cases:
+        V = len(w)
+        parts = mvs.view_partition_weighted(w, n)
+        assert len(parts) == n and parts[0][0] == 0 and parts[-1][1] == V
+        assert all(a[1] == b[0] for a, b in zip(parts, parts[1:])) and all(lo <= hi for lo, hi in parts)
+        got = max(sum(w[lo:hi]) for lo, hi in parts)
+        best = min(max(sum(w[a:b]) for a, b in zip((0,) + cuts, cuts + (V,)))
+                   for cuts in itertools.combinations_with_replacement(range(V + 1), n - 1))
+        assert got == best, (w, n, parts)
+        if V >= n:
+            assert all(hi > lo for lo, hi in parts), "a rank left without a view although there are enough"
+    # the 15-view grid on 8 GPUs, work counted in neighbour views only: the heaviest rank carries 13 instead of the
+    # even split's 16
+    num = mvs.make_subsets(5, 3)[1]
+    load = lambda parts: max(sum(int(k) for k in num[lo:hi]) for lo, hi in parts)    # noqa: E731
+    assert load(mvs.view_partition_weighted([int(k) for k in num], 8)) == 13
+    assert load([mvs.view_partition(15, 8, r) for r in range(8)]) == 16
+    with pytest.raises(mvs.MvsError):
+        mvs.view_partition_weighted([3, 0, 2], 2)
+    with pytest.raises(mvs.MvsError):
+        mvs.exchange_plan(4, 2, *mvs.make_subsets(2, 2), parts=[(0, 3), (2, 4)])

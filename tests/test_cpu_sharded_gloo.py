@@ -22,11 +22,16 @@ from cl_multiview_stereo_b200 import synth  # noqa: E402
 
 @pytest.mark.parametrize("aw,ah,nh,nv", [(5, 3, 1, 1), (4, 4, 1, 1), (5, 5, 1, 1), (3, 3, 2, 1), (2, 4, 1, 1), (7, 1, 1, 1)])
 @pytest.mark.parametrize("n", [1, 2, 3, 4, 8])
-def test_exchange_plan_delivers_every_needed_view_once(aw, ah, nh, nv, n):
+@pytest.mark.parametrize("weighted", [False, True])
+def test_exchange_plan_delivers_every_needed_view_once(aw, ah, nh, nv, n, weighted):
     V = aw * ah
     sub, num = mvs.make_subsets(aw, ah, nh, nv)
-    plan = mvs.exchange_plan(V, n, sub, num)
-    parts = [mvs.view_partition(V, n, r) for r in range(n)]
+    if weighted:
+        parts = mvs.view_partition_weighted(mvs.view_weights(num), n)
+        plan = mvs.exchange_plan(V, n, sub, num, parts)
+    else:
+        plan = mvs.exchange_plan(V, n, sub, num)
+        parts = [mvs.view_partition(V, n, r) for r in range(n)]
     owner = {v: r for r, (lo, hi) in enumerate(parts) for v in range(lo, hi)}
     assert sorted(owner) == list(range(V))
     got = {}
