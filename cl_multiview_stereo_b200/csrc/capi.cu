@@ -619,7 +619,9 @@ static int exchange_plan(int V, int nranks, const int *part, const int *view_sub
     return 0;
 }
 
-static int exchange_raw(mvs_frame *f, char *base, size_t per_view)
+// `count` buffers go out in ONE group (one launch, one synchronisation with the neighbour ranks); transfers between
+// a pair of ranks are matched in issue order, which is the same plan order on both sides
+static int exchange_raw_multi(mvs_frame *f, int count, char *const *base, const size_t *per_view)
 {
     mvs_ctx *c = f->ctx;
     if (!c->comm || c->nranks == 1) return 0;
@@ -627,14 +629,17 @@ static int exchange_raw(mvs_frame *f, char *base, size_t per_view)
     build_exchange_plan(f->d.V, c->nranks, f->part.empty() ? nullptr : f->part.data(), f->h_subset.data(),
                         f->h_subset_num.data(), t);
     NK(GroupStart());
-    for (size_t i = 0; i + 2 < t.size(); i += 3) {
-        const int v = t[i], src = t[i + 1], dst = t[i + 2];
-        if (src == c->rank) NK(Send(base + per_view * v, per_view, ncclChar, dst, c->comm, c->stream));
-        if (dst == c->rank) NK(Recv(base + per_view * v, per_view, ncclChar, src, c->comm, c->stream));
-    }
+    for (int b = 0; b < count; ++b)
+        for (size_t i = 0; i + 2 < t.size(); i += 3) {
+            const int v = t[i], src = t[i + 1], dst = t[i + 2];
+            if (src == c->rank) NK(Send(base[b] + per_view[b] * v, per_view[b], ncclChar, dst, c->comm, c->stream));
+            if (dst == c->rank) NK(Recv(base[b] + per_view[b] * v, per_view[b], ncclChar, src, c->comm, c->stream));
+        }
     NK(GroupEnd());
     return 0;
 }
+
+static int exchange_raw(mvs_frame *f, char *base, size_t per_view) { return exchange_raw_multi(f, 1, &base, &per_view); }
 
 // views this rank reads but does not own
 static void halo_views(mvs_frame *f, std::vector<int> &out)
@@ -717,11 +722,14 @@ extern "C" int mvs_frame_slic(mvs_frame *f)
 static int exchange_after_slic(mvs_frame *f)
 {
     if (!f->ctx->comm || f->ctx->nranks == 1) return 0;
-    if (mvs_frame_exchange(f, MVS_BUF_RGBX) || mvs_frame_exchange(f, MVS_BUF_IDX) || mvs_frame_exchange(f, MVS_BUF_MAP))
-        return 1;
+    CK(cudaSetDevice(f->ctx->device));
+    StageTimer t(f, ST_EXCH);
+    // image, labels and centres of the halo views in one group (three groups cost two more waits on the neighbours)
+    char *base[3] = {(char *)f->d.rgbx, (char *)f->d.idx, (char *)f->d.map};
+    const size_t per_view[3] = {sizeof(uchar4) * (size_t)f->d.N, sizeof(uint32_t) * (size_t)f->d.N, 32 * (size_t)f->d.M};
+    if (exchange_raw_multi(f, 3, base, per_view)) return 1;
     std::vector<int> halo;
     halo_views(f, halo);
-    StageTimer t(f, ST_EXCH);
     for (int v : halo) f->ctx->launches += launch_cvt(f->d, v, v + 1, f->ctx->stream);
     return check_launch("halo cvt");
 }
