@@ -35,9 +35,27 @@ SYMBOLS = [
     "mvs_frame_stage_ms", "mvs_frame_set_timing", "mvs_slic_run", "mvs_bm_run", "mvs_refine_run",
     "mvs_frame_view_fusion", "mvs_view_fusion_run", "mvs_frame_upload_bgr", "mvs_frame_export_u8",
     "mvs_frame_draw_segmentation", "mvs_view_partition_weighted", "mvs_exchange_plan_for", "mvs_frame_set_partition",
+    "mvs_frame_propagate_stats", "mvs_draw_segmentation_run",
 ]
 
 _lib = None
+
+
+def _check_fresh():
+    """refuse a library that was not built from the sources beside it (the .so is git-ignored and travels to the
+    GPU box prebuilt: this is what ties it to the commit).  MVS_ALLOW_STALE=1 skips the check."""
+    if os.environ.get("MVS_ALLOW_STALE"):
+        return
+    from . import build as b
+    stamp = LIB_PATH + ".srchash"
+    if not os.path.exists(stamp):
+        raise MvsError(f"{stamp} is missing: rebuild with `python -m cl_multiview_stereo_b200.build`")
+    have = open(stamp).read().split()
+    cu, deps = b.native_sources()
+    want = b._source_hash(cu + deps)
+    if not have or have[0] != want:
+        raise MvsError(f"{LIB_PATH} was built from other sources (hash {have[0][:12] if have else '?'}, "
+                       f"tree {want[:12]}): rebuild with `python -m cl_multiview_stereo_b200.build`")
 
 
 def lib():
@@ -47,6 +65,7 @@ def lib():
             raise MvsError(
                 f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                 "(nvcc, sm_100a).  There is no CPU fallback.")
+        _check_fresh()
         _lib = C.CDLL(LIB_PATH)
         _lib.mvs_last_error.restype = C.c_char_p
         for s in SYMBOLS:

@@ -133,6 +133,12 @@ class Context:
         check(lib().mvs_comm_init(self._h, buf, int(nranks), int(rank)))
 
 
+def device_count():
+    n = C.c_int()
+    check(lib().mvs_device_count(C.byref(n)))
+    return n.value
+
+
 def view_partition(V, nranks, rank):
     lo, hi = C.c_int(), C.c_int()
     check(lib().mvs_view_partition(int(V), int(nranks), int(rank), C.byref(lo), C.byref(hi)))
@@ -304,6 +310,13 @@ class Frame:
 
     def propagate(self, it):
         check(lib().mvs_frame_propagate(self._h, int(it)))
+
+    def propagate_stats(self, it):
+        """one propagate iteration with work counters (diagnostic)"""
+        st = (C.c_ulonglong * 12)()
+        check(lib().mvs_frame_propagate_stats(self._h, int(it), st))
+        return dict(zip(("superpixels", "candidates", "unique_planes", "cache_probes", "cache_misses", "items",
+                         "items_inside", "items_visible", "samples_inside", "samples_visible"), [int(x) for x in st]))
 
     def fusion(self):
         check(lib().mvs_frame_fusion(self._h))

@@ -34,14 +34,61 @@ def _newer(target, sources):
     return any(os.path.getmtime(s) > t for s in sources)
 
 
+def _source_hash(paths):
+    """sha256 over the named sources (name + contents): recorded beside the library and checked when it is loaded"""
+    import hashlib
+    h = hashlib.sha256()
+    for q in sorted(paths):
+        h.update(os.path.basename(q).encode() + b"\0")
+        with open(q, "rb") as fh:
+            h.update(fh.read())
+        h.update(b"\0")
+    return h.hexdigest()
+
+
+def native_sources():
+    cu = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith(".cu")]
+    deps = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith(".cuh")]
+    deps.append(os.path.join(ROOT, "include", "mvs_capi.h"))
+    return cu, deps
+
+
 def build_native(force=False, verbose=False):
-    cu = [os.path.join(CSRC, f) for f in ("slic.cu", "photo.cu", "refine.cu", "propagate.cu", "fuse.cu", "io.cu", "capi.cu")]
-    deps = cu + [os.path.join(CSRC, f) for f in ("common.cuh", "mvs_math.cuh")] + [os.path.join(ROOT, "include", "mvs_capi.h")]
-    if force or _newer(LIB, deps):
-        cmd = [_nvcc()] + NVCC_FLAGS + ["-shared", "-o", LIB] + cu + ["-ldl"]
+    """every .cu -> build/<name>.o (in parallel, only what changed), linked into libmvs_b200.so; the hash of the
+    sources the library was built from is written to libmvs_b200.so.srchash (_native.lib() refuses a stale one).
+    MVS_NVCC_DEFS adds -D switches (kernel experiments on the GPU box)."""
+    cu, deps = native_sources()
+    extra = os.environ.get("MVS_NVCC_DEFS", "").split()
+    want = _source_hash(cu + deps) + (" " + " ".join(extra) if extra else "")
+    stamp = LIB + ".srchash"
+    have = open(stamp).read().strip() if os.path.exists(stamp) else ""
+    if force or have != want or not os.path.exists(LIB):
+        odir = os.path.join(ROOT, "build")
+        os.makedirs(odir, exist_ok=True)
+        procs = []
+        objs = []
+        for src in cu:
+            obj = os.path.join(odir, os.path.basename(src)[:-3] + ".o")
+            objs.append(obj)
+            tag = obj + ".srchash"
+            w = _source_hash([src] + deps) + " " + " ".join(extra)
+            if not force and os.path.exists(obj) and os.path.exists(tag) and open(tag).read() == w:
+                continue
+            cmd = [_nvcc()] + NVCC_FLAGS + extra + ["-c", "-o", obj, src]
+            if verbose:
+                print(" ".join(cmd))
+            procs.append((subprocess.Popen(cmd), tag, w, cmd))
+        for pr, tag, w, cmd in procs:
+            if pr.wait() != 0:
+                raise subprocess.CalledProcessError(pr.returncode, cmd)
+            with open(tag, "w") as fh:
+                fh.write(w)
+        cmd = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB] + objs + ["-ldl"]
         if verbose:
             print(" ".join(cmd))
         subprocess.check_call(cmd)
+        with open(stamp, "w") as fh:
+            fh.write(want + "\n")
     host_src = sorted(os.path.join(HOST, f) for f in os.listdir(HOST) if f.endswith(".cpp")) if os.path.isdir(HOST) else []
     if host_src:
         hdeps = host_src + [os.path.join(ROOT, "include", f) for f in os.listdir(os.path.join(ROOT, "include"))]

@@ -110,7 +110,8 @@ struct mvs_frame {
     std::vector<cudaEvent_t> ev;   // pairs (start, stop) tagged with a stage
     std::vector<int> ev_stage;
     size_t ev_used = 0;
-    bool timing = true;
+    bool timing = false;           // per-stage CUDA events are opt-in (mvs_frame_set_timing)
+    std::string timer_err;         // first failure of an event call inside a StageTimer
 };
 
 extern "C" const char *mvs_last_error(void) { return g_err.c_str(); }
@@ -357,14 +358,17 @@ static void prepare_refine(mvs_frame *f, float gamma_, float alpha_, float fuse_
 extern "C" int mvs_frame_destroy(mvs_frame *f)
 {
     if (!f) return 0;
-    cudaSetDevice(f->ctx->device);
-    cudaStreamSynchronize(f->ctx->stream);
+    cudaError_t first = cudaSetDevice(f->ctx->device);
+    auto keep = [&](cudaError_t e) { if (first == cudaSuccess && e != cudaSuccess) first = e; };
+    keep(cudaStreamSynchronize(f->ctx->stream));
     FrameDev &d = f->d;
-    cudaFree(d.rgbx); cudaFree(d.lab); cudaFree(d.idx); cudaFree(d.idx_tmp); cudaFree(d.map); cudaFree(d.rep);
-    cudaFree(d.flat); cudaFree(d.disp); cudaFree(d.disp_proj); cudaFree(d.disp_fused); cudaFree(d.io_stage); cudaFree(d.view_subset); cudaFree(d.subset_num); cudaFree(d.levels);
-    for (int k = 0; k < 2; ++k) { cudaFree(d.plane[k]); cudaFree(d.cost[k]); cudaFree(d.state6[k]); }
-    for (cudaEvent_t e : f->ev) cudaEventDestroy(e);
+    void *bufs[] = {d.rgbx, d.lab, d.idx, d.idx_tmp, d.map, d.rep, d.flat, d.disp, d.pixd, d.disp_proj, d.disp_fused,
+                    d.io_stage, d.view_subset, d.subset_num, d.levels, d.plane[0], d.plane[1], d.cost[0], d.cost[1],
+                    d.state6[0], d.state6[1], d.edge, d.pixcol};
+    for (void *p : bufs) if (p) keep(cudaFree(p));
+    for (cudaEvent_t e : f->ev) keep(cudaEventDestroy(e));
     delete f;
+    if (first != cudaSuccess) return fail("mvs_frame_destroy: %s", cudaGetErrorString(first));
     return 0;
 }
 
@@ -386,7 +390,13 @@ static int frame_alloc(mvs_ctx *ctx, int W, int H, int S, int aw, int ah, bool n
     if ((double)d.M >= 16777216.0) { delete f; return fail("more than 2^24 superpixels per view"); }
     size_t VN = (size_t)d.V * d.N, VM = (size_t)d.V * d.M;
     cudaError_t e = cudaSuccess;
-    auto A = [&](void **p, size_t bytes) { if (e == cudaSuccess) { e = cudaMalloc(p, bytes); if (e == cudaSuccess) e = cudaMemsetAsync(*p, 0, bytes, ctx->stream); } };
+    size_t asked = 0;
+    auto A = [&](void **p, size_t bytes) {
+        if (e != cudaSuccess) return;
+        asked += bytes;
+        e = cudaMalloc(p, bytes);
+        if (e == cudaSuccess) e = cudaMemsetAsync(*p, 0, bytes, ctx->stream);
+    };
     if (need_rgbx) A((void **)&d.rgbx, VN * 4);
     if (need_lab) A((void **)&d.lab, VN * 16);
     A((void **)&d.idx, VN * 4);
@@ -398,7 +408,12 @@ static int frame_alloc(mvs_ctx *ctx, int W, int H, int S, int aw, int ah, bool n
     if (need_disp) A((void **)&d.disp, VN * 4);
     A((void **)&d.view_subset, sizeof(int) * d.V * d.V);
     A((void **)&d.subset_num, sizeof(int) * d.V);
-    if (e != cudaSuccess) { mvs_frame_destroy(f); return fail("frame allocation failed: %s", cudaGetErrorString(e)); }
+    if (e != cudaSuccess) {
+        std::string why = cudaGetErrorString(e);
+        cudaGetLastError();
+        mvs_frame_destroy(f);
+        return fail("frame allocation failed after %.1f MB (%d views of %dx%d): %s", asked / 1e6, aw * ah, W, H, why.c_str());
+    }
     f->lo = 0; f->hi = d.V;
     *out = f;
     return 0;
@@ -496,6 +511,12 @@ extern "C" int mvs_frame_download_async(mvs_frame *f, int which, int v0, int v1,
 }
 
 // ---- stage timing -----------------------------------------------------------------------
+// Off by default (mvs_frame_set_timing).  Every timed stage call takes one (start, stop) event pair from the
+// frame's pool; mvs_frame_stage_ms() sums them per stage and hands the pairs back.  The pool is bounded: a caller
+// that loops over mvs_frame_run without ever reading the times stops being timed after MAX_TIMED_PAIRS pairs
+// instead of growing without bound.  A failing event call is remembered and reported by the stage that made it.
+static const size_t MAX_TIMED_PAIRS = 1024;
+
 struct StageTimer {
     mvs_frame *f;
     bool on;
@@ -503,19 +524,33 @@ struct StageTimer {
     {
         if (!on) return;
         if (f->ev_used + 2 > f->ev.size()) {
-            cudaEvent_t a, b;
-            cudaEventCreate(&a); cudaEventCreate(&b);
+            if (f->ev.size() >= 2 * MAX_TIMED_PAIRS) { on = false; return; }
+            cudaEvent_t a = nullptr, b = nullptr;
+            cudaError_t e = cudaEventCreate(&a);
+            if (e == cudaSuccess) e = cudaEventCreate(&b);
+            if (e != cudaSuccess) {
+                if (a) cudaEventDestroy(a);
+                note(e, "cudaEventCreate");
+                on = false;
+                return;
+            }
             f->ev.push_back(a); f->ev.push_back(b);
             f->ev_stage.push_back(stage); f->ev_stage.push_back(stage);
         }
         f->ev_stage[f->ev_used] = stage;
-        cudaEventRecord(f->ev[f->ev_used], f->ctx->stream);
+        cudaError_t e = cudaEventRecord(f->ev[f->ev_used], f->ctx->stream);
+        if (e != cudaSuccess) { note(e, "cudaEventRecord"); on = false; }
     }
     ~StageTimer()
     {
         if (!on) return;
-        cudaEventRecord(f->ev[f->ev_used + 1], f->ctx->stream);
+        cudaError_t e = cudaEventRecord(f->ev[f->ev_used + 1], f->ctx->stream);
+        if (e != cudaSuccess) { note(e, "cudaEventRecord"); return; }   // the pair is not counted
         f->ev_used += 2;
+    }
+    void note(cudaError_t e, const char *what)
+    {
+        if (f->timer_err.empty()) f->timer_err = std::string(what) + ": " + cudaGetErrorString(e);
     }
 };
 
@@ -546,6 +581,18 @@ static int check_launch(const char *what)
 {
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail("%s: kernel launch failed: %s", what, cudaGetErrorString(e));
+    return 0;
+}
+
+// after a timed stage: a failed event call inside its StageTimer is this stage's error
+static int check_stage(mvs_frame *f, const char *what)
+{
+    if (check_launch(what)) return 1;
+    if (!f->timer_err.empty()) {
+        std::string m = f->timer_err;
+        f->timer_err.clear();
+        return fail("%s: stage timing failed: %s", what, m.c_str());
+    }
     return 0;
 }
 
@@ -629,13 +676,17 @@ static int exchange_raw_multi(mvs_frame *f, int count, char *const *base, const 
     build_exchange_plan(f->d.V, c->nranks, f->part.empty() ? nullptr : f->part.data(), f->h_subset.data(),
                         f->h_subset_num.data(), t);
     NK(GroupStart());
-    for (int b = 0; b < count; ++b)
-        for (size_t i = 0; i + 2 < t.size(); i += 3) {
+    ncclResult_t bad = ncclSuccess;
+    for (int b = 0; b < count && bad == ncclSuccess; ++b)
+        for (size_t i = 0; i + 2 < t.size() && bad == ncclSuccess; i += 3) {
             const int v = t[i], src = t[i + 1], dst = t[i + 2];
-            if (src == c->rank) NK(Send(base[b] + per_view[b] * v, per_view[b], ncclChar, dst, c->comm, c->stream));
-            if (dst == c->rank) NK(Recv(base[b] + per_view[b] * v, per_view[b], ncclChar, src, c->comm, c->stream));
+            if (src == c->rank) bad = g_nccl.Send(base[b] + per_view[b] * v, per_view[b], ncclChar, dst, c->comm, c->stream);
+            if (dst == c->rank && bad == ncclSuccess)
+                bad = g_nccl.Recv(base[b] + per_view[b] * v, per_view[b], ncclChar, src, c->comm, c->stream);
         }
-    NK(GroupEnd());
+    ncclResult_t end = g_nccl.GroupEnd();   // the group is closed on every path
+    if (bad != ncclSuccess) return fail("halo exchange: NCCL error %d (%s)", (int)bad, g_nccl.GetErrorString(bad));
+    if (end != ncclSuccess) return fail("halo exchange: NCCL error %d (%s) in ncclGroupEnd", (int)end, g_nccl.GetErrorString(end));
     return 0;
 }
 
@@ -714,7 +765,7 @@ extern "C" int mvs_frame_slic(mvs_frame *f)
         if (!f->d.idx_tmp) return fail("connectivity buffer not allocated");
         L += launch_connectivity(f->d, f->lo, f->hi, st);
     }
-    return check_launch("slic");
+    return check_stage(f, "slic");
 }
 
 // after SLIC on a sharded frame: ship RGBX (4 B/px) + labels + centres of the halo views and
@@ -748,7 +799,7 @@ extern "C" int mvs_frame_block_match(mvs_frame *f)
         StageTimer t(f, ST_BM);
         f->ctx->launches += launch_block_match(f->d, f->bl_ratio, f->lo, f->hi, st);
     }
-    return check_launch("block_match");
+    return check_stage(f, "block_match");
 }
 
 extern "C" int mvs_frame_flatness(mvs_frame *f)
@@ -757,7 +808,7 @@ extern "C" int mvs_frame_flatness(mvs_frame *f)
     CK(cudaSetDevice(f->ctx->device));
     StageTimer t(f, ST_FLAT);
     f->ctx->launches += launch_flatness(f->d, f->gamma_flat, f->lo, f->hi, f->ctx->stream);
-    return check_launch("flatness");
+    return check_stage(f, "flatness");
 }
 
 extern "C" int mvs_frame_init_state(mvs_frame *f)
@@ -767,10 +818,27 @@ extern "C" int mvs_frame_init_state(mvs_frame *f)
     StageTimer t(f, ST_INIT);
     RefineArgs a{f->gamma, f->alpha, f->fuse, f->bl_ratio, f->kernel_step, f->kss, 0};
     f->ctx->launches += launch_init_state(f->d, a, f->lo, f->hi, f->ctx->stream);
-    return check_launch("init_state");
+    return check_stage(f, "init_state");
 }
 
-extern "C" int mvs_frame_propagate(mvs_frame *f, int iter)
+// contiguous runs of the views this rank's propagate reads: its own range plus the halo views
+static void read_view_runs(mvs_frame *f, std::vector<std::pair<int, int>> &runs)
+{
+    std::vector<int> halo;
+    halo_views(f, halo);
+    std::vector<char> need(f->d.V, 0);
+    for (int v = f->lo; v < f->hi; ++v) need[v] = 1;
+    for (int v : halo) need[v] = 1;
+    for (int v = 0; v < f->d.V;) {
+        if (!need[v]) { ++v; continue; }
+        int e = v;
+        while (e < f->d.V && need[e]) ++e;
+        runs.push_back({v, e});
+        v = e;
+    }
+}
+
+static int propagate_impl(mvs_frame *f, int iter, unsigned long long *stats_dev)
 {
     if (!f) return fail("null frame");
     if (iter < 0) return fail("negative iteration");
@@ -778,16 +846,49 @@ extern "C" int mvs_frame_propagate(mvs_frame *f, int iter)
     int src = iter & 1, dst = src ^ 1;   // even: A -> B, odd: B -> A (depth_refinement.cpp:744-753)
     if (f->ctx->comm && f->ctx->nranks > 1)
         if (mvs_frame_exchange(f, src ? MVS_BUF_STATE_B : MVS_BUF_STATE_A)) return 1;
+    if (!f->d.pixd) CK(cudaMalloc(&f->d.pixd, sizeof(uint2) * (size_t)f->d.V * f->d.N));
     StageTimer t(f, ST_PROP);
+    // per-pixel {label, input-plane disparity} of every view this rank's superpixels project into
+    std::vector<std::pair<int, int>> runs;
+    read_view_runs(f, runs);
+    if (propagate_needs() == 2 && (iter == 0 || !f->d.pixcol)) {   // colours are fixed from block matching on
+        if (!f->d.pixcol) CK(cudaMalloc(&f->d.pixcol, sizeof(float4) * (size_t)f->d.V * f->d.N));
+        for (auto &r : runs) f->ctx->launches += launch_pixel_colour(f->d, r.first, r.second, f->ctx->stream);
+    }
+    for (auto &r : runs) f->ctx->launches += launch_pixel_plane(f->d, src, r.first, r.second, f->ctx->stream);
     // per-iteration arguments, depth_refinement.cpp:768-769 (int / int, float / int)
     RefineArgs a{f->gamma, f->alpha, f->fuse, f->bl_ratio, f->kernel_step / (iter + 1), f->kss / (float)(iter + 1), iter};
-    int nl = launch_propagate(f->d, a, src, dst, f->lo, f->hi, f->ctx->stream);
+    int nl = launch_propagate(f->d, a, src, dst, f->lo, f->hi, f->ctx->stream, stats_dev);
     if (nl == -3) return fail("propagate: %d views of %d pixels exceed the 2^31 pixels one frame may hold", f->d.V, f->d.N);
     if (nl == -2) return fail("propagate: kernel_step %d gives more than 255 candidate planes per superpixel", a.no_kernel_steps);
     if (nl < 0) return fail("propagate: kernel_step %d with %d neighbour views needs more shared memory than one SM has",
                             a.no_kernel_steps, f->d.max_neighbours);
     f->ctx->launches += nl;
-    return check_launch("propagate");
+    return check_stage(f, "propagate");
+}
+
+extern "C" int mvs_frame_propagate(mvs_frame *f, int iter) { return propagate_impl(f, iter, nullptr); }
+
+// One propagate iteration with work counters (a diagnostic, not part of mvs_frame_run): stats12 =
+// {superpixels, candidate planes, unique planes evaluated, similarity-cache probes, cache misses, (plane, view)
+// items, items with samples inside the neighbour image, items with a visible sample, samples inside, samples visible}.
+// How many of a superpixel's candidates are bit-identical duplicates depends on the scene; the bench
+// line reports it so that a frame rate can be read against the work it stands for.
+extern "C" int mvs_frame_propagate_stats(mvs_frame *f, int iter, unsigned long long *stats12)
+{
+    if (!f || !stats12) return fail("null argument");
+    CK(cudaSetDevice(f->ctx->device));
+    unsigned long long *dev = nullptr;
+    CK(cudaMalloc(&dev, 12 * sizeof(unsigned long long)));
+    cudaError_t e = cudaMemsetAsync(dev, 0, 12 * sizeof(unsigned long long), f->ctx->stream);
+    int rc = e != cudaSuccess ? fail("cudaMemsetAsync: %s", cudaGetErrorString(e)) : propagate_impl(f, iter, dev);
+    if (!rc) {
+        e = cudaMemcpyAsync(stats12, dev, 12 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, f->ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(f->ctx->stream);
+        if (e != cudaSuccess) rc = fail("propagate_stats: %s", cudaGetErrorString(e));
+    }
+    cudaFree(dev);
+    return rc;
 }
 
 extern "C" int mvs_frame_fusion(mvs_frame *f)
@@ -798,7 +899,7 @@ extern "C" int mvs_frame_fusion(mvs_frame *f)
     StageTimer t(f, ST_FUSION);
     // fusion always reads buffer A (depth_refinement.cpp:1352)
     f->ctx->launches += launch_spixl_to_image(f->d, 0, f->lo, f->hi, f->ctx->stream);
-    return check_launch("fusion");
+    return check_stage(f, "fusion");
 }
 
 // Multi-view fusion of the disparity images (clcode.cl:1995-2101; host sequence
@@ -816,22 +917,32 @@ extern "C" int mvs_frame_view_fusion(mvs_frame *f)
     if (!d.disp_fused) { CK(cudaMalloc(&d.disp_fused, bytes)); }
     cudaStream_t st = f->ctx->stream;
     mvs_ctx *c = f->ctx;
-    if (c->comm && c->nranks > 1 && (f->lo != 0 || f->hi != d.V)) {
+    if (c->comm && c->nranks > 1) {
+        // Every rank of the communicator takes this branch, whatever it owns, so that the transfers pair up: rank
+        // s sends its own images to rank r exactly when both hold views (a rank without views votes nothing and
+        // needs no images; a rank that owns every view still serves the others).
         StageTimer t(f, ST_EXCH);
         std::vector<int> lo(c->nranks), hi(c->nranks);
         for (int r = 0; r < c->nranks; ++r) {
             if (f->part.empty()) mvs_view_partition(d.V, c->nranks, r, &lo[r], &hi[r]);
             else { lo[r] = f->part[2 * r]; hi[r] = f->part[2 * r + 1]; }
         }
+        if (lo[c->rank] != f->lo || hi[c->rank] != f->hi)
+            return fail("view fusion: frame holds views [%d,%d), the partition gives rank %d [%d,%d)", f->lo, f->hi, c->rank,
+                        lo[c->rank], hi[c->rank]);
         const size_t per_view = sizeof(float) * (size_t)d.N;
+        const bool mine = hi[c->rank] > lo[c->rank];
         NK(GroupStart());
-        for (int r = 0; r < c->nranks; ++r) {
-            if (r == c->rank) continue;
-            if (hi[c->rank] > lo[c->rank])
-                NK(Send((char *)d.disp + per_view * lo[c->rank], per_view * (hi[c->rank] - lo[c->rank]), ncclChar, r, c->comm, st));
-            if (hi[r] > lo[r]) NK(Recv((char *)d.disp + per_view * lo[r], per_view * (hi[r] - lo[r]), ncclChar, r, c->comm, st));
+        ncclResult_t bad = ncclSuccess;
+        for (int r = 0; r < c->nranks && bad == ncclSuccess && mine; ++r) {
+            if (r == c->rank || hi[r] <= lo[r]) continue;
+            bad = g_nccl.Send((char *)d.disp + per_view * lo[c->rank], per_view * (hi[c->rank] - lo[c->rank]), ncclChar, r, c->comm, st);
+            if (bad == ncclSuccess)
+                bad = g_nccl.Recv((char *)d.disp + per_view * lo[r], per_view * (hi[r] - lo[r]), ncclChar, r, c->comm, st);
         }
-        NK(GroupEnd());
+        ncclResult_t end = g_nccl.GroupEnd();   // the group is closed on every path
+        if (bad != ncclSuccess) return fail("view fusion exchange: NCCL error %d (%s)", (int)bad, g_nccl.GetErrorString(bad));
+        if (end != ncclSuccess) return fail("view fusion exchange: NCCL error %d (%s) in ncclGroupEnd", (int)end, g_nccl.GetErrorString(end));
     } else if (f->lo != 0 || f->hi != d.V) {
         return fail("view fusion reads every view: frame holds views [%d,%d) of %d and has no communicator", f->lo, f->hi, d.V);
     }
@@ -841,7 +952,7 @@ extern "C" int mvs_frame_view_fusion(mvs_frame *f)
     int nl = launch_view_fusion(d, f->bl_ratio, f->fuse, f->lo, f->hi, st);
     if (nl < 0) return fail("view fusion: %d views need more shared memory than one SM has", d.V);
     f->ctx->launches += nl;
-    return check_launch("view_fusion");
+    return check_stage(f, "view_fusion");
 }
 
 extern "C" int mvs_frame_refine(mvs_frame *f)
@@ -961,6 +1072,22 @@ extern "C" int mvs_slic_run(mvs_ctx *ctx, int width, int height, int spixl_size,
              (lab && mvs_frame_download_async(f, MVS_BUF_LAB, 0, count, lab)) ||
              (map && mvs_frame_download_async(f, MVS_BUF_MAP, 0, count, map)) ||
              (idx && mvs_frame_download_async(f, MVS_BUF_IDX, 0, count, idx)) || mvs_ctx_sync(ctx);
+    mvs_frame_destroy(f);
+    return rc;
+}
+
+// clSLIC::draw_segmentation_lines (clSLIC.cpp:447-478) with host arrays: `count` images + their labels in, the
+// overlay written into out_rgbx (in/out: its one-pixel frame and pad bytes are kept, as in the reference)
+extern "C" int mvs_draw_segmentation_run(mvs_ctx *ctx, int width, int height, int count, const uint32_t *idx,
+                                         const void *in_rgbx, void *out_rgbx)
+{
+    if (!idx || !in_rgbx || !out_rgbx) return fail("null argument");
+    if (count <= 0) return fail("count must be positive");
+    mvs_frame *f = nullptr;
+    // only the per-pixel image / label buffers matter here; S = 8 sizes the (unused) superpixel arrays
+    if (frame_alloc(ctx, width, height, width < 8 || height < 8 ? 6 : 8, count, 1, true, false, false, false, &f)) return 1;
+    int rc = mvs_frame_upload_async(f, MVS_BUF_RGBX, 0, count, in_rgbx) || mvs_frame_upload_async(f, MVS_BUF_IDX, 0, count, idx) ||
+             mvs_frame_draw_segmentation(f, 0, count, (uint8_t *)out_rgbx);
     mvs_frame_destroy(f);
     return rc;
 }

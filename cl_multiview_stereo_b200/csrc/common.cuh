@@ -21,8 +21,12 @@ struct FrameDev {
     float2 *cost[2];    // [V][M]   {sm,cs}
     float *state6[2];   // [V][M][6] API layout, filled on export
     float *disp;        // [V][N]
+    uint2 *pixd;        // [V][N]   {label, disparity of the label's INPUT plane at the pixel}: what propagate's consistency
+                        //          walk gathers per sample (rebuilt before every iteration; allocated on demand)
     float *disp_proj;   // [V][N]   multi-view fusion: chased disparity (allocated on demand)
     float *disp_fused;  // [V][N]   multi-view fusion: voted disparity (allocated on demand)
+    float4 *pixcol;     // [V][N]   {L, a, b, 0} of the pixel's superpixel (only when propagate_needs() == 2; on demand)
+    float *edge;        // [V][N]   edge-aware SLIC: Sobel magnitude of Lab (edge_enable; allocated on demand)
     uint8_t *io_stage;  // [V][N][4] staging of packed BGR input / 8-bit and overlay output (allocated on demand)
     int *view_subset;   // [V][V]
     int *subset_num;    // [V]
@@ -56,8 +60,12 @@ int launch_block_match(const FrameDev &f, float bl_ratio, int z0, int z1, cudaSt
 
 int launch_flatness(const FrameDev &f, float gamma_flat, int z0, int z1, cudaStream_t st);
 int launch_init_state(const FrameDev &f, const RefineArgs &a, int z0, int z1, cudaStream_t st);
-int launch_propagate(const FrameDev &f, const RefineArgs &a, int src, int dst, int z0, int z1, cudaStream_t st);
+int launch_propagate(const FrameDev &f, const RefineArgs &a, int src, int dst, int z0, int z1, cudaStream_t st,
+                     unsigned long long *stats = nullptr);
 int launch_spixl_to_image(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);
+int launch_pixel_plane(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);
+int launch_pixel_colour(const FrameDev &f, int z0, int z1, cudaStream_t st);
+int propagate_needs();
 int launch_view_fusion(const FrameDev &f, float bl_ratio, float fuse, int z0, int z1, cudaStream_t st);
 int launch_ingest_bgr(const FrameDev &f, const void *bgr_dev, int z0, int z1, cudaStream_t st);
 int launch_quantise_disp(const FrameDev &f, const float *src, uint8_t *out_dev, float mn, float range, int z0, int z1,

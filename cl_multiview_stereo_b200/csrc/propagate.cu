@@ -29,6 +29,7 @@
 #include "common.cuh"
 #include "mvs_math.cuh"
 #include <stdlib.h>
+#include <string.h>
 #include <algorithm>
 
 namespace mvs {
@@ -39,6 +40,22 @@ constexpr int PR_WARPS = 4;                 // warps per CTA (tile rows)
 constexpr int PR_OCT = 4;                   // octets per warp (tile columns)
 constexpr int PR_SPB = PR_WARPS * PR_OCT;   // superpixels per CTA
 constexpr int PR_UB = 4;                    // unique planes evaluated per batch
+// build-time knobs (MVS_NVCC_DEFS): resident CTAs the register allocation aims for; where the colour of the
+// superpixel under a projected sample comes from (PR_COL 0: the 32-byte centre record of the label the pixel
+// record carries, a dependent gather; 1: that gather behind a per-superpixel cache of similarities, kept as a
+// measured rejection; 2: a per-pixel colour image gathered beside the pixel record, no dependent gather)
+#ifndef PR_MINB
+#define PR_MINB 6
+#endif
+#ifndef PR_COL
+#define PR_COL 0
+#endif
+#ifndef PR_SIMC_SLOTS
+#define PR_SIMC_SLOTS 32
+#endif
+constexpr int PR_SIMC = PR_COL == 1 ? PR_SIMC_SLOTS : 0;   // slots of a superpixel's colour-similarity cache
+static_assert(PR_COL != 1 || (PR_SIMC >= 16 && (PR_SIMC & (PR_SIMC - 1)) == 0), "cache slots: a power of two, at least 16");
+constexpr int PR_HP = 2;                    // planes whose smoothness products are staged at a time (phases G, H)
 
 struct PArgs {
     const float4 *map;        // [V][M][2]
@@ -46,6 +63,8 @@ struct PArgs {
     const uint2 *rep;         // [V][M]
     const float2 *flat;       // [V][M]
     const int *view_subset, *subset_num;
+    const uint2 *pixd;        // [V][N] {label, input-plane disparity at the pixel} (k_pixel_plane)
+    const float4 *pixcol;     // [V][N] {L, a, b, 0} of the pixel's superpixel (k_pixel_colour; PR_COL 2)
     const float4 *plane_in;   // [V][M] {d,nx,ny,nz}
     const float2 *cost_in;    // [V][M] {sm,cs}
     float4 *plane_out;
@@ -58,24 +77,29 @@ struct PArgs {
     int tmax;                 // smoothness terms per superpixel at most (8 + 4K)
     int ncmax;                // candidate slots per superpixel at most (valid neighbours + far + 8 pairs)
     int nsmax;                // neighbour views per view at most (8 on a grid with neib_hor = neib_ver = 1)
+    unsigned mw_magic;        // ceil(2^32 / mw): label -> approximate map row for the cache hash
+    unsigned long long *stats;   // optional counters {superpixels, candidates, unique planes, cache probes, cache misses}
 };
 
 // shared-memory record of one superpixel (dynamic part sized by tmax / ncmax)
 struct SpLayout {
-    int meta, tab, cp, cc, cw, own, uniq, sres, stage, total;
+    int meta, tab, cp, cc, cw, own, uniq, sres, stage, simc, total;
 };
 
+// CTA layout: float4 viewt[nsmax] (one table: every superpixel of a CTA belongs to the same view), then one
+// record of L.total bytes per superpixel
 __host__ __device__ inline SpLayout sp_layout(int tmax, int ncmax, int nsmax)
 {
     SpLayout L;
-    int o = 9 * 16 + nsmax * 16;              // samp[9], viewt[nsmax]
+    int o = 9 * 16;                           // samp[9]
     L.meta = o;  o += 16;                     // {L, a, b} of the own centre (read by whichever lane samples for it)
     L.tab = o;   o += 16 * tmax;              // float4 tab[tmax]
     L.cp = o;    o += 16 * ncmax;             // float4 candidate planes
     L.cc = o;    o += 8 * ncmax;              // float2 costs of the unique ones
     L.sres = o;  o += 8 * PR_UB * nsmax;      // float2 per (plane, view): {term, flags}
-    const int prod_bytes = 4 * PR_UB * (tmax + 1), sdi_bytes = 16 * PR_UB * 9;
+    const int prod_bytes = 4 * PR_HP * (tmax + 1), sdi_bytes = 16 * PR_UB * 9;
     L.stage = o; o += ((prod_bytes > sdi_bytes ? prod_bytes : sdi_bytes) + 15) & ~15;   // sdi (E,F) then prod (G,H)
+    L.simc = o;  o += 8 * PR_SIMC;            // {key, similarity} cache (PR_COL 1)
     L.cw = o;    o += 4 * ncmax;              // float acceptance weight (colour similarity to the source)
     L.own = o;   o += ncmax;                  // u8: slot whose costs this candidate takes
     L.uniq = o;  o += ncmax;                  // u8: slots of the unique planes, in order
@@ -123,7 +147,10 @@ __device__ __forceinline__ bool same_bits(const float4 &p, const float4 &q)
 // Then round(d * dv) == dv * round(d) exactly (dv in {-1, 0, 1}; holds for inf / NaN too), and
 // the two rounds of a sample are taken once per (plane, sample) instead of once per view.
 // NP: gamma >= 0 and alpha >= 0 (checked by the launcher), so every exp argument -(d*d)*w is <= 0 or NaN
-template <bool UNIT, int MINB, bool NP>
+// PIXD: the consistency walk gathers the per-pixel {label, plane disparity} record of k_pixel_plane and keeps the
+// colour similarities of the superpixels it meets in a small per-superpixel cache (false: the walk of the first
+// round of this kernel, label -> centre record + plane, kept for A/B measurement: MVS_PROP_MODE=legacy)
+template <bool UNIT, int MINB, bool NP, bool PIXD, bool STATS>
 __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
 {
     extern __shared__ __align__(16) unsigned char pr_smem[];
@@ -137,9 +164,10 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     const bool live = x < a.mw && y < a.mh;
 
     const SpLayout L = sp_layout(a.tmax, a.ncmax, a.nsmax);
-    unsigned char *sbase = pr_smem + (size_t)(warp * PR_OCT + (lane >> 3)) * L.total;
+    float4 *viewt = reinterpret_cast<float4 *>(pr_smem);         // {view * N (int bits), dvx, dvy, view * M (int bits)}
+    unsigned char *sp_smem = pr_smem + 16 * a.nsmax;
+    unsigned char *sbase = sp_smem + (size_t)(warp * PR_OCT + (lane >> 3)) * L.total;
     float4 *samp = reinterpret_cast<float4 *>(sbase);            // {sx, sy (integers held as float), cx - sx, cy - sy}
-    float4 *viewt = samp + 9;                                    // {view * N (int bits), dvx, dvy, view * M (int bits)}
     float4 *tab = reinterpret_cast<float4 *>(sbase + L.tab);     // {cx-cxq, cy-cyq, d_q, similarity}
     float4 *cp = reinterpret_cast<float4 *>(sbase + L.cp);       // candidate planes {d, nx, ny, nz}
     float2 *cc = reinterpret_cast<float2 *>(sbase + L.cc);       // {smoothness, consistency}
@@ -160,6 +188,11 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     const float cx = ma.y, cy = ma.z, cL = ma.w, ca = mb.x, cb = mb.y;
     const float2 fl = a.flat[zM + sp];
     if (l8 == 0) *reinterpret_cast<float4 *>(sbase + L.meta) = make_float4(cL, ca, cb, 0.0f);
+    if (PIXD && PR_COL == 1) {   // empty cache: no key has view number 255
+        unsigned long long *simc = reinterpret_cast<unsigned long long *>(sbase + L.simc);
+#pragma unroll
+        for (int k = l8; k < PR_SIMC; k += 8) simc[k] = 0xFFFFFFFFull;
+    }
     const int ns = live ? a.subset_num[z] : 0;
     const int camx = z % a.aw, camy = z / a.aw;
     const double half_fly = 0.5 * (double)fl.y;   // clcode.cl:1621 is a double expression
@@ -177,12 +210,16 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
             // |sx|, |sy| < 2^24: the float copies are exact
             samp[k] = make_float4((float)sx, (float)sy, cx - (float)sx, cy - (float)sy);
         }
-        for (int n = l8; n < ns; n += 8) {
+    }
+    // the CTA's view table: the first warp fills it, the block barrier publishes it (no lane has left the kernel:
+    // octets outside the map stay as idle members of their warp)
+    if (warp == 0)
+        for (int n = lane; n < nsw; n += 32) {
             int view = a.view_subset[a.V * z + n];
             viewt[n] = make_float4(__int_as_float(view * a.N), (float)(view % a.aw - camx),
                                    (float)(view / a.aw - camy), __int_as_float(view * a.M));
         }
-    }
+    __syncthreads();
 
     // ---- smoothness term table (candidate-invariant part of compute_smoothness) ----
     // slot order = the reference's accumulation order: 8 near neighbours, then for
@@ -295,62 +332,158 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                 const int n = (int)(((unsigned long long)(unsigned)it * nbt_inv) >> 24), r = it - n * nbt;
                 const int oc = (r >= nb0) + (r >= q1) + (r >= q2);
                 const int u = r - (oc == 0 ? 0 : oc == 1 ? nb0 : oc == 2 ? q1 : q2);
-                const unsigned char *ob = pr_smem + (size_t)(warp * PR_OCT + oc) * L.total;
+                const unsigned char *ob = sp_smem + (size_t)(warp * PR_OCT + oc) * L.total;
                 const float4 *samp = reinterpret_cast<const float4 *>(ob);
                 const float4 *sdi = reinterpret_cast<const float4 *>(ob + L.stage);
                 float2 *sres = reinterpret_cast<float2 *>(const_cast<unsigned char *>(ob) + L.sres);
                 const float4 own = *reinterpret_cast<const float4 *>(ob + L.meta);
                 const float cL = own.x, ca = own.y, cb = own.z;
-                const float4 vt = samp[9 + n];   // that octet's view table (an octet outside the map has none)
+                const float4 vt = viewt[n];
                 const uint32_t nbase = (uint32_t)__float_as_int(vt.x), mbase = (uint32_t)__float_as_int(vt.w);
                 float num = 0.0f, vws = 0.0f, ows = 0.0f, visibility = 0.0f, visible = 0.0f;
-                // three samples at a time: their label gathers, then their centre / plane gathers, are
-                // issued together (a sample that projects outside reads pixel 0 and is masked afterwards)
+                if (PIXD) {
+                    // Per sample ONE 8-byte gather: the label at the projected pixel and the disparity of that
+                    // superpixel's input plane there (k_pixel_plane) -- no centre / plane gathers, no division.
+                    // The colour of that superpixel (for the similarity to the own colour) comes, by PR_COL, from its
+                    // centre record (a second, dependent gather), from that gather behind a per-superpixel cache of
+                    // similarities, or from a per-pixel colour image gathered beside the pixel record.
+#if PR_COL == 1
+                    // direct-mapped cache, key = view slot << 24 | q.  A hit returns the bits the computation gives.
+                    // Volatile 64-bit accesses: key and value must travel together -- split into two 32-bit loads, a
+                    // hit could pair its key with the value another lane stores in between.
+                    volatile unsigned long long *simc =
+                        reinterpret_cast<volatile unsigned long long *>(const_cast<unsigned char *>(ob) + L.simc);
+                    const uint32_t keyn = (uint32_t)n << 24;
+                    const int hn = (n & (PR_SIMC / 16 - 1)) << 4;
+#endif
+                    int n_vis = 0;
 #pragma unroll 1
-                for (int k0 = 0; k0 < 9; k0 += 3) {
-                    int pix[3];
-                    float fxp[3], fyp[3], dik[3];
-                    bool inb[3];
+                    for (int k0 = 0; k0 < 9; k0 += 3) {
+                        int pix[3];
+                        float dik[3];
+                        bool inb[3];
 #pragma unroll
-                    for (int j = 0; j < 3; ++j) {
-                        const float4 sd = sdi[u * 9 + k0 + j];
-                        const float4 sv = samp[k0 + j];
-                        int xp, yp;
-                        if (UNIT) {
-                            xp = f2i(sv.x - sd.z * vt.y);
-                            yp = f2i(sv.y - sd.w * vt.z);
-                        } else {
-                            xp = f2i(sv.x - round_haz(sd.x * vt.y));   // clcode.cl:1576-1577
-                            yp = f2i(sv.y - round_haz(sd.y * vt.z));
+                        for (int j = 0; j < 3; ++j) {
+                            const float4 sd = sdi[u * 9 + k0 + j];
+                            const float4 sv = samp[k0 + j];
+                            int xp, yp;
+                            if (UNIT) {
+                                xp = f2i(sv.x - sd.z * vt.y);
+                                yp = f2i(sv.y - sd.w * vt.z);
+                            } else {
+                                xp = f2i(sv.x - round_haz(sd.x * vt.y));   // clcode.cl:1576-1577
+                                yp = f2i(sv.y - round_haz(sd.y * vt.z));
+                            }
+                            inb[j] = (unsigned)xp < (unsigned)a.W && (unsigned)yp < (unsigned)a.H;
+                            pix[j] = inb[j] ? yp * a.W + xp : 0;
+                            dik[j] = sd.x;
                         }
-                        inb[j] = (unsigned)xp < (unsigned)a.W && (unsigned)yp < (unsigned)a.H;
-                        pix[j] = inb[j] ? yp * a.W + xp : 0;
-                        fxp[j] = (float)xp; fyp[j] = (float)yp; dik[j] = sd.x;
+                        uint2 pr[3];
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) pr[j] = __ldg(a.pixd + nbase + (uint32_t)pix[j]);
+#if PR_COL == 2
+                        float4 col[3];
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) col[j] = __ldg(a.pixcol + nbase + (uint32_t)pix[j]);
+#elif PR_COL == 0
+                        Rec8 rec[3];
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) rec[j] = ld_rec8(a.map + 2 * (mbase + pr[j].x));
+#endif
+#pragma unroll
+                        for (int j = 0; j < 3; ++j)
+                            if (inb[j]) {
+                                const float diff = __uint_as_float(pr[j].y) - dik[j];
+                                if (fabsf(diff) < a.fuse) { visible += expf_pinned<NP>(-diff * diff * a.alpha); vws += 1.0f; if (STATS) n_vis++; }
+                                else { if (diff != diff) visible += diff; ows += 1.0f; }
+                                float sim;
+#if PR_COL == 2
+                                {
+                                    const float cdiff = dist3(col[j].x, col[j].y, col[j].z, cL, ca, cb);
+                                    sim = expf_pinned<NP>(-cdiff * cdiff * a.gamma);
+                                }
+#elif PR_COL == 0
+                                {
+                                    const float cdiff = dist3(rec[j].L, rec[j].a, rec[j].b, cL, ca, cb);
+                                    sim = expf_pinned<NP>(-cdiff * cdiff * a.gamma);
+                                }
+#else
+                                {
+                                    const uint32_t q = pr[j].x;
+                                    const uint32_t qy = __umulhi(q, a.mw_magic), qx = q - qy * (uint32_t)a.mw;
+                                    volatile unsigned long long *slot = simc + (hn | ((qy & 3u) << 2) | (qx & 3u));
+                                    const unsigned long long e = *slot;   // {key (low word), similarity bits}
+                                    if (STATS) atomicAdd(a.stats + 3, 1ull);
+                                    if ((uint32_t)e == (keyn | q)) sim = __uint_as_float((uint32_t)(e >> 32));
+                                    else {
+                                        if (STATS) atomicAdd(a.stats + 4, 1ull);
+                                        const Rec8 r = ld_rec8(a.map + 2 * (mbase + q));
+                                        const float cdiff = dist3(r.L, r.a, r.b, cL, ca, cb);
+                                        sim = expf_pinned<NP>(-cdiff * cdiff * a.gamma);
+                                        *slot = ((unsigned long long)__float_as_uint(sim) << 32) | (keyn | q);
+                                    }
+                                }
+#endif
+                                visibility += sim;
+                                num += 1.0f;
+                            }
                     }
-                    uint32_t vq[3];
-#pragma unroll
-                    for (int j = 0; j < 3; ++j) vq[j] = mbase + a.idx[nbase + (uint32_t)pix[j]];
-                    float qcx[3], qcy[3], qL[3], qA[3], qB[3];
-                    float4 pl[3];
-#pragma unroll
-                    for (int j = 0; j < 3; ++j) {
-                        // one 256-bit gather instead of a 128-bit + a 64-bit one: 17.8 -> 16.1 ms per frame
-                        const Rec8 r = ld_rec8(a.map + 2 * vq[j]);
-                        qcx[j] = r.cx; qcy[j] = r.cy; qL[j] = r.L; qA[j] = r.a; qB[j] = r.b;
-                        pl[j] = a.plane_in[vq[j]];
+                    if (STATS) {   // (plane, view) items: all / with samples / with a visible sample; samples: inside / visible
+                        atomicAdd(a.stats + 5, 1ull);
+                        if (num > 0.0f) atomicAdd(a.stats + 6, 1ull);
+                        if (vws > 0.0f) atomicAdd(a.stats + 7, 1ull);
+                        atomicAdd(a.stats + 8, (unsigned long long)num);
+                        atomicAdd(a.stats + 9, (unsigned long long)n_vis);
                     }
+                } else {
+                    // three samples at a time: their label gathers, then their centre / plane gathers, are
+                    // issued together (a sample that projects outside reads pixel 0 and is masked afterwards)
+#pragma unroll 1
+                    for (int k0 = 0; k0 < 9; k0 += 3) {
+                        int pix[3];
+                        float fxp[3], fyp[3], dik[3];
+                        bool inb[3];
 #pragma unroll
-                    for (int j = 0; j < 3; ++j)
-                        if (inb[j]) {
-                            const float d_proj = (pl[j].y * (qcx[j] - fxp[j]) + pl[j].z * (qcy[j] - fyp[j]) + pl[j].w * pl[j].x) / pl[j].w;
-                            const float diff = d_proj - dik[j];
-                            // visible += when_visible * exp(..): 0 * exp is +0 unless diff is NaN
-                            if (fabsf(diff) < a.fuse) { visible += expf_pinned<NP>(-diff * diff * a.alpha); vws += 1.0f; }
-                            else { if (diff != diff) visible += diff; ows += 1.0f; }
-                            const float cdiff = dist3(qL[j], qA[j], qB[j], cL, ca, cb);
-                            visibility += expf_pinned<NP>(-cdiff * cdiff * a.gamma);
-                            num += 1.0f;
+                        for (int j = 0; j < 3; ++j) {
+                            const float4 sd = sdi[u * 9 + k0 + j];
+                            const float4 sv = samp[k0 + j];
+                            int xp, yp;
+                            if (UNIT) {
+                                xp = f2i(sv.x - sd.z * vt.y);
+                                yp = f2i(sv.y - sd.w * vt.z);
+                            } else {
+                                xp = f2i(sv.x - round_haz(sd.x * vt.y));   // clcode.cl:1576-1577
+                                yp = f2i(sv.y - round_haz(sd.y * vt.z));
+                            }
+                            inb[j] = (unsigned)xp < (unsigned)a.W && (unsigned)yp < (unsigned)a.H;
+                            pix[j] = inb[j] ? yp * a.W + xp : 0;
+                            fxp[j] = (float)xp; fyp[j] = (float)yp; dik[j] = sd.x;
                         }
+                        uint32_t vq[3];
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) vq[j] = mbase + a.idx[nbase + (uint32_t)pix[j]];
+                        float qcx[3], qcy[3], qL[3], qA[3], qB[3];
+                        float4 pl[3];
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) {
+                            // one 256-bit gather instead of a 128-bit + a 64-bit one: 17.8 -> 16.1 ms per frame
+                            const Rec8 r = ld_rec8(a.map + 2 * vq[j]);
+                            qcx[j] = r.cx; qcy[j] = r.cy; qL[j] = r.L; qA[j] = r.a; qB[j] = r.b;
+                            pl[j] = a.plane_in[vq[j]];
+                        }
+#pragma unroll
+                        for (int j = 0; j < 3; ++j)
+                            if (inb[j]) {
+                                const float d_proj = (pl[j].y * (qcx[j] - fxp[j]) + pl[j].z * (qcy[j] - fyp[j]) + pl[j].w * pl[j].x) / pl[j].w;
+                                const float diff = d_proj - dik[j];
+                                // visible += when_visible * exp(..): 0 * exp is +0 unless diff is NaN
+                                if (fabsf(diff) < a.fuse) { visible += expf_pinned<NP>(-diff * diff * a.alpha); vws += 1.0f; }
+                                else { if (diff != diff) visible += diff; ows += 1.0f; }
+                                const float cdiff = dist3(qL[j], qA[j], qB[j], cL, ca, cb);
+                                visibility += expf_pinned<NP>(-cdiff * cdiff * a.gamma);
+                                num += 1.0f;
+                            }
+                    }
                 }
                 float term = 0.0f;
                 int flags = 0;   // bit0: view has samples, bit1: some visible, bit2: some occluded
@@ -362,40 +495,45 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                 sres[u * a.nsmax + n] = make_float2(term, __int_as_float(flags));
             }
             __syncwarp();   // sdi is dead from here on: prod reuses its storage
+            // G + H, PR_HP planes at a time (their products share the storage sdi had: staging all PR_UB planes at once
+            // would make `prod` the largest array of a superpixel's record and cost a resident CTA).
             // G: compute_smoothness products, terms spread over the octet (pooling these over the warp like the
-            // consistency items costs more in index arithmetic than it saves: 15.2 -> 15.8 ms)
-            for (int u = 0; u < nb; ++u) {
-                const float4 pl = cp[uniq[b0 + u]];
-                for (int t = l8; t < T; t += 8) {
-                    const float4 e = tab[t];
-                    const float d_intrp = (pl.y * e.x + pl.z * e.y + pl.w * pl.x) / pl.w;   // clcode.cl:1426-1428
-                    const float diff = d_intrp - e.z;
-                    prod[u * pstride + t] = e.w * expf_pinned<NP>(-diff * diff * a.alpha);
-                }
-            }
-            __syncwarp();
+            //    consistency items costs more in index arithmetic than it saves: 15.2 -> 15.8 ms)
             // H: ordered sums, one lane per plane: views in subset order, then the smoothness terms
-            if (l8 < nb) {
-                float consistency = 0.0f;
-                int view_counter = 0;
-                for (int n = 0; n < ns; ++n) {   // clcode.cl:1614-1622
-                    const float2 rn = sres[l8 * a.nsmax + n];
-                    const int fn = __float_as_int(rn.y);
-                    if (fn & 1) {
-                        view_counter++;
-                        if (fn & 2) consistency += rn.x;
-                        if (fn & 4) consistency = (float)((double)consistency + half_fly);
+            for (int h0 = 0; __any_sync(FULL, h0 < nb); h0 += PR_HP) {
+                const int h1 = min(h0 + PR_HP, nb);
+                for (int u = h0; u < h1; ++u) {
+                    const float4 pl = cp[uniq[b0 + u]];
+                    for (int t = l8; t < T; t += 8) {
+                        const float4 e = tab[t];
+                        const float d_intrp = (pl.y * e.x + pl.z * e.y + pl.w * pl.x) / pl.w;   // clcode.cl:1426-1428
+                        const float diff = d_intrp - e.z;
+                        prod[(u - h0) * pstride + t] = e.w * expf_pinned<NP>(-diff * diff * a.alpha);
                     }
                 }
-                const float margin = (float)0.01;
-                const float cs1 = view_counter > 0 ? fmaxf(margin, consistency / (float)view_counter) : margin;
-                float smoothness = 0.0f;
-                const float *pr = prod + l8 * pstride;
-                for (int t = 0; t < T; ++t) smoothness += pr[t];
-                const float sm1 = weight_norm > 0.0f ? smoothness / weight_norm : (float)0.000001;
-                cc[uniq[b0 + l8]] = make_float2(sm1, cs1);
+                __syncwarp();
+                if (l8 >= h0 && l8 < h1) {
+                    float consistency = 0.0f;
+                    int view_counter = 0;
+                    for (int n = 0; n < ns; ++n) {   // clcode.cl:1614-1622
+                        const float2 rn = sres[l8 * a.nsmax + n];
+                        const int fn = __float_as_int(rn.y);
+                        if (fn & 1) {
+                            view_counter++;
+                            if (fn & 2) consistency += rn.x;
+                            if (fn & 4) consistency = (float)((double)consistency + half_fly);
+                        }
+                    }
+                    const float margin = (float)0.01;
+                    const float cs1 = view_counter > 0 ? fmaxf(margin, consistency / (float)view_counter) : margin;
+                    float smoothness = 0.0f;
+                    const float *pr = prod + (l8 - h0) * pstride;
+                    for (int t = 0; t < T; ++t) smoothness += pr[t];
+                    const float sm1 = weight_norm > 0.0f ? smoothness / weight_norm : (float)0.000001;
+                    cc[uniq[b0 + l8]] = make_float2(sm1, cs1);
+                }
+                __syncwarp();
             }
-            __syncwarp();
         }
     };
 
@@ -487,21 +625,34 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     if (live && l8 == 0) {
         a.plane_out[zM + sp] = make_float4(pd, pnx, pny, pnz);
         a.cost_out[zM + sp] = make_float2(psm, pcs);
+        if (STATS) {   // candidates / unique planes evaluated (both rounds)
+            atomicAdd(a.stats + 0, 1ull);
+            atomicAdd(a.stats + 1, (unsigned long long)c_hi);
+            atomicAdd(a.stats + 2, (unsigned long long)UQ);
+        }
     }
 }
 
-int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, int z0, int z1, cudaStream_t st)
+// what the consistency walk reads beside the frame's own arrays: 1 = the per-pixel record (k_pixel_plane of the
+// input state, every iteration), 2 = also the per-pixel colour image (k_pixel_colour, once per frame)
+int propagate_needs() { return PR_COL == 2 ? 2 : 1; }
+
+int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, int z0, int z1, cudaStream_t st,
+                     unsigned long long *stats)
 {
     if (z1 <= z0) return 0;
     PArgs a;
     a.map = f.map; a.idx = f.idx; a.rep = f.rep; a.flat = f.flat;
     a.view_subset = f.view_subset; a.subset_num = f.subset_num;
+    a.pixd = f.pixd; a.pixcol = f.pixcol;
     a.plane_in = f.plane[src]; a.cost_in = f.cost[src]; a.plane_out = f.plane[dst]; a.cost_out = f.cost[dst];
     a.V = f.V; a.W = f.W; a.H = f.H; a.mw = f.mw; a.mh = f.mh; a.N = f.N; a.M = f.M; a.aw = f.aw;
     a.gamma = r.gamma; a.alpha = r.alpha; a.bl_ratio = r.bl_ratio; a.fuse = r.fuse;
     a.K = r.no_kernel_steps < 0 ? 0 : r.no_kernel_steps;
     a.kernel_step_size = r.kernel_step_size; a.iter = r.iter; a.z0 = z0;
     a.tmax = 8 + 4 * a.K;
+    a.mw_magic = (unsigned)((0x100000000ULL + (unsigned)f.mw - 1) / (unsigned)f.mw);
+    a.stats = stats;
     // candidate slots a superpixel can fill: 8 neighbours, the far neighbours whose offset fits the map
     // (same float -> int conversion as the kernel: truncation, saturating), 8 pairs
     long long stride = (long long)r.kernel_step_size;
@@ -520,21 +671,31 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     if (a.ncmax > 255) return -2;   // slot numbers are kept in bytes
     a.nsmax = std::max(1, f.max_neighbours);
     const SpLayout L = sp_layout(a.tmax, a.ncmax, a.nsmax);
-    size_t smem = (size_t)PR_SPB * L.total;
+    size_t smem = 16 * (size_t)a.nsmax + (size_t)PR_SPB * L.total;
     if ((double)f.V * f.N >= 2147483648.0) return -3;   // 32-bit gather offsets
     if (smem > 227 * 1024) return -1;
     // every neighbour at most one camera apart?  (host copy of the lists lives with the frame)
-    bool unit = f.unit_baseline != 0;
+    const bool unit = f.unit_baseline != 0;
     dim3 g((f.mw + PR_OCT - 1) / PR_OCT, z1 - z0, (f.mh + PR_WARPS - 1) / PR_WARPS);
     const bool np = a.gamma >= 0.0f && a.alpha >= 0.0f;
-#define PR_LAUNCH(U, B, P)                                                                                       \
+    // the per-pixel record path needs f.pixd (k_pixel_plane of the SAME input state) and view slots below 255
+    static const bool legacy = [] { const char *e = getenv("MVS_PROP_MODE"); return e && !strcmp(e, "legacy"); }();
+    const bool pixd = !legacy && f.pixd && a.nsmax < 255 && (PR_COL != 2 || f.pixcol);
+#define PR_LAUNCH(U, B, P, X, S)                                                                                 \
     do {                                                                                                         \
-        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        k_propagate<U, B, P><<<g, PR_WARPS * 32, smem, st>>>(a);                                                 \
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B, P, X, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        k_propagate<U, B, P, X, S><<<g, PR_WARPS * 32, smem, st>>>(a);                                           \
     } while (0)
-    if (!unit) { if (np) PR_LAUNCH(false, 5, true); else PR_LAUNCH(false, 5, false); }
-    else if (np) PR_LAUNCH(true, 5, true);
-    else PR_LAUNCH(true, 5, false);
+#define PR_PICK(U, P)                                                                                            \
+    do {                                                                                                         \
+        if (!pixd) PR_LAUNCH(U, 5, P, false, false);                                                             \
+        else if (stats) PR_LAUNCH(U, PR_MINB, P, true, true);                                                          \
+        else PR_LAUNCH(U, PR_MINB, P, true, false);                                                                    \
+    } while (0)
+    if (!unit) { if (np) PR_PICK(false, true); else PR_PICK(false, false); }
+    else if (np) PR_PICK(true, true);
+    else PR_PICK(true, false);
+#undef PR_PICK
 #undef PR_LAUNCH
     return 1;
 }

@@ -273,6 +273,88 @@ int launch_spixl_to_image(const FrameDev &f, int src, int z0, int z1, cudaStream
 }
 
 // ---------------------------------------------------------------------------------------
+// Per-pixel record of a state: {label, d} with d = the plane of the pixel's superpixel evaluated at
+// the pixel.  compute_consistency (clcode.cl:1581-1600) looks up, for every reprojected sample, the
+// label at the projected pixel, that superpixel's centre and its INPUT plane, and evaluates
+//   d_intrp_proj = (n.x*(c.x - xp) + n.y*(c.y - yp) + n.z*d) / n.z
+// -- a pure function of (view, pixel) for a fixed input state, the same for every candidate plane of
+// every superpixel that lands on the pixel.  It is therefore evaluated ONCE per pixel and iteration
+// here (same expression, same operand order, same bits) and k_propagate gathers one 8-byte record per
+// sample instead of label -> (32-byte centre record, 16-byte plane) -> 8 flops and an IEEE division.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_pixel_plane(const float4 *__restrict__ map, const uint32_t *__restrict__ idx,
+                                                     const float4 *__restrict__ plane, uint2 *__restrict__ pixd,
+                                                     int W, int H, int N, int M, int z0)
+{
+    int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+    int z = z0 + blockIdx.z;
+    if (x >= W || y >= H) return;
+    size_t pi = (size_t)z * N + (size_t)y * W + x;
+    uint32_t q = idx[pi];
+    float4 a = map[2 * ((size_t)z * M + q)];
+    float4 pl = plane[(size_t)z * M + q];
+    float d = (pl.y * (a.y - (float)x) + pl.z * (a.z - (float)y) + pl.w * pl.x) / pl.w;
+    pixd[pi] = make_uint2(q, __float_as_uint(d));
+}
+
+__global__ void __launch_bounds__(256) k_pixel_plane4(const float4 *__restrict__ map, const uint4 *__restrict__ idx4,
+                                                      const float4 *__restrict__ plane, uint4 *__restrict__ pixd4,
+                                                      int W, int H, int N, int M, int z0)
+{
+    const int xq = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+    const int z = z0 + blockIdx.z;
+    const int x = 4 * xq;
+    if (x >= W || y >= H) return;
+    const size_t pq = ((size_t)z * N + (size_t)y * W + x) / 4;
+    const uint4 q4 = idx4[pq];
+    const uint32_t q[4] = {q4.x, q4.y, q4.z, q4.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float4 a = map[2 * ((size_t)z * M + q[k])];
+        const float4 pl = plane[(size_t)z * M + q[k]];
+        o[k] = __float_as_uint((pl.y * (a.y - (float)(x + k)) + pl.z * (a.z - (float)y) + pl.w * pl.x) / pl.w);
+    }
+    pixd4[2 * pq] = make_uint4(q[0], o[0], q[1], o[1]);
+    pixd4[2 * pq + 1] = make_uint4(q[2], o[2], q[3], o[3]);
+}
+
+// per-pixel colour of the pixel's superpixel (constant over the refinement; an experiment knob of k_propagate)
+__global__ void __launch_bounds__(256) k_pixel_colour(const float4 *__restrict__ map, const uint32_t *__restrict__ idx,
+                                                      float4 *__restrict__ pixcol, int W, int H, int N, int M, int z0)
+{
+    int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+    int z = z0 + blockIdx.z;
+    if (x >= W || y >= H) return;
+    size_t pi = (size_t)z * N + (size_t)y * W + x;
+    uint32_t q = idx[pi];
+    float4 a = map[2 * ((size_t)z * M + q)], b = map[2 * ((size_t)z * M + q) + 1];
+    pixcol[pi] = make_float4(a.w, b.x, b.y, 0.0f);
+}
+
+int launch_pixel_colour(const FrameDev &f, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    dim3 b(32, 8), g((f.W + 31) / 32, (f.H + 7) / 8, z1 - z0);
+    k_pixel_colour<<<g, b, 0, st>>>(f.map, f.idx, f.pixcol, f.W, f.H, f.N, f.M, z0);
+    return 1;
+}
+
+int launch_pixel_plane(const FrameDev &f, int src, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    dim3 b(32, 8);
+    if (f.W % 4 == 0) {
+        dim3 g((f.W / 4 + 31) / 32, (f.H + 7) / 8, z1 - z0);
+        k_pixel_plane4<<<g, b, 0, st>>>(f.map, (const uint4 *)f.idx, f.plane[src], (uint4 *)f.pixd, f.W, f.H, f.N, f.M, z0);
+    } else {
+        dim3 g((f.W + 31) / 32, (f.H + 7) / 8, z1 - z0);
+        k_pixel_plane<<<g, b, 0, st>>>(f.map, f.idx, f.plane[src], f.pixd, f.W, f.H, f.N, f.M, z0);
+    }
+    return 1;
+}
+
+// ---------------------------------------------------------------------------------------
 // 6-float API layout <-> internal plane/cost split
 // ---------------------------------------------------------------------------------------
 __global__ void k_export_state(const float4 *__restrict__ plane, const float2 *__restrict__ cost,

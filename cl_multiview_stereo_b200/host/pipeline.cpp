@@ -87,7 +87,8 @@ void pipeline::run_device_resident()
     disp_img.resize(N);
     state_a_.resize(6 * M);
     if (multi_view_fusion) disp_fused_.resize(N);
-    int rc = mvs_frame_upload_async(f, MVS_BUF_RGBX, 0, view_num, in_img.data()) || mvs_frame_run(f) ||
+    int rc = mvs_frame_set_timing(f, 1) ||   // pipeline::stage_ms reports the split of this run
+             mvs_frame_upload_async(f, MVS_BUF_RGBX, 0, view_num, in_img.data()) || mvs_frame_run(f) ||
              (multi_view_fusion && (mvs_frame_view_fusion(f) ||
                                     mvs_frame_download_async(f, MVS_BUF_DISP_FUSED, 0, view_num, disp_fused_.data()))) ||
              mvs_frame_download_async(f, MVS_BUF_LAB, 0, view_num, cvt_img) ||

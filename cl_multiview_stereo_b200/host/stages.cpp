@@ -54,20 +54,13 @@ void clSLIC::do_super_pixel_seg(vec3u *in_img, vec3f *cvt_img, vec8f *spixl_map,
     do_super_pixel_seg_batch(1, in_img, cvt_img, spixl_map, idx_img);
 }
 
-// host-side overlay (clSLIC.cpp:447-478): interior pixels whose 4-neighbourhood holds another
-// label become {0,0,255}; the 1-pixel frame of out_img is left untouched, as in the reference
+// overlay (clSLIC.cpp:447-478) on the device: interior pixels whose 4-neighbourhood holds another label become
+// {0,0,255}, the others take in_img; the 1-pixel frame of out_img is left untouched, as in the reference
 void clSLIC::draw_segmentation_lines(cl_uchar3 *in_img, cl_uchar3 *out_img)
 {
     if (!last_idx) throw std::runtime_error("draw_segmentation_lines: no segmentation has been computed yet");
-    const int h = img_size.y, w = img_size.x;
-    const cl_uint *L = last_idx;
-    for (int i = 1; i < h - 1; i++)
-        for (int j = 1; j < w - 1; j++) {
-            size_t p = (size_t)i * w + j;
-            bool edge = L[p] != L[p + 1] || L[p] != L[p - 1] || L[p] != L[p - w] || L[p] != L[p + w];
-            if (edge) { out_img[p].s0 = 0; out_img[p].s1 = 0; out_img[p].s2 = 255; }
-            else { out_img[p].s0 = in_img[p].s0; out_img[p].s1 = in_img[p].s1; out_img[p].s2 = in_img[p].s2; }
-        }
+    must(mvs_draw_segmentation_run(need_ctx(program, "clSLIC"), img_size.x, img_size.y, 1, last_idx, in_img, out_img),
+         "clSLIC::draw_segmentation_lines");
 }
 
 // ---- clPhotoConsistency ----------------------------------------------------------------------

@@ -141,6 +141,10 @@ int mvs_frame_refine(mvs_frame *f);
 int mvs_frame_flatness(mvs_frame *f);
 int mvs_frame_init_state(mvs_frame *f);
 int mvs_frame_propagate(mvs_frame *f, int iter);
+/* one propagate iteration with work counters (diagnostic): stats12 = {superpixels, candidate planes, unique planes
+ * evaluated, similarity-cache probes, cache misses, (plane, view) items, items with samples inside the neighbour
+ * image, items with a visible sample, samples inside, visible samples, 0, 0} */
+int mvs_frame_propagate_stats(mvs_frame *f, int iter, unsigned long long *stats12);
 int mvs_frame_fusion(mvs_frame *f);
 /* multi-view fusion: project_to_reference_inv + remove_view_inconsistency per reference view
  * (clcode.cl:1995-2101) in the host sequence the reference keeps disabled (depth_refinement.cpp:1382-1451),
@@ -164,6 +168,10 @@ int mvs_frame_set_timing(mvs_frame *f, int enable);
 int mvs_slic_run(mvs_ctx *ctx, int width, int height, int spixl_size, float color_weight, int no_iter,
                  int enforce_connectivity, int count, const void *rgbx, void *lab, void *map, uint32_t *idx);
 
+/* clSLIC::draw_segmentation_lines (clSLIC.h:20, clSLIC.cpp:447-478) on the device: `count` images [count][H][W]
+ * vec3u + their labels in; out_rgbx is in/out (interior pixels are rewritten, the one-pixel frame is kept). */
+int mvs_draw_segmentation_run(mvs_ctx *ctx, int width, int height, int count, const uint32_t *idx, const void *in_rgbx,
+                              void *out_rgbx);
 /* clPhotoConsistency::do_initial_depth_estimation (photo_consistency.h:10-19, .cpp:21-150).
  * view_subset is the flattened int[V*V] (row stride V) and subset_num int[V] the reference
  * builds at photo_consistency.cpp:39-47.  Fills rep and map[].s7. */

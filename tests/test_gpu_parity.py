@@ -146,6 +146,7 @@ def test_full_pipeline_matches_oracle(ctx, oracle, aw, ah, W, H, seed):
     f = mvs.Frame(ctx, s, W, H)
     try:
         f.upload(mvs.BUF_RGBX, rgbx)
+        f.set_timing(True)   # per-stage CUDA events are opt-in
         f.run()
         assert np.array_equal(f.download(mvs.BUF_IDX), ref["idx"])
         assert np.array_equal(f.download(mvs.BUF_REP), ref["rep"])
@@ -456,6 +457,7 @@ def test_wide_neighbourhoods_match_oracle(ctx, oracle, aw, ah, nh, nv, W, H):
     f = mvs.Frame(ctx, s, W, H)
     try:
         f.upload(mvs.BUF_RGBX, rgbx)
+        f.set_timing(True)   # per-stage CUDA events are opt-in
         f.run()
         assert np.array_equal(f.download(mvs.BUF_IDX), ref["idx"])
         assert_bits_equal(f.download(mvs.BUF_MAP), ref["map"], "map (initial disparities)")

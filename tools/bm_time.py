@@ -16,6 +16,7 @@ def main():
     ctx = mvs.Context(0)
     f = mvs.Frame(ctx, s, W, H)
     f.upload(mvs.BUF_RGBX, rgbx)
+    f.set_timing(True)
     f.slic()
     f.block_match()
     ctx.sync(); f.stage_ms()
