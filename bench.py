@@ -33,7 +33,15 @@ WORKLOADS = {
     "4x4_1080p": (1920, 1080, 4, 4),
     "5x5_4k": (3840, 2160, 5, 5),
     "tiny": (192, 128, 3, 2),
+    # the reference's own data (tests/data/_ref, copied from /root/reference/Images by tests/data/fetch_bundled.py)
+    "bundled_15view": (1920, 1080, 5, 3),          # c0f1..c14f1 (backup/data-bar.txt), shipped literals
+    "bundled_15view_legacy": (1920, 1080, 5, 3),   # same views, the legacy 15-view settings (levels 10..100 step 2, bl 0.625)
+    "beer_garden_3x3": (1920, 1080, 3, 3),         # Images/Beer-Garden/img0..8 (data.txt), shipped literals
+    # no structure at all: independent uniform noise in every view (block matching returns arbitrary levels, so
+    # neighbouring superpixels rarely share a plane: the candidate dedup of k_propagate has nothing to skip)
+    "noise_15view_1080p": (1920, 1080, 5, 3),
 }
+BUNDLED = {"bundled_15view": "bar15", "bundled_15view_legacy": "bar15", "beer_garden_3x3": "beer9"}
 
 
 def settings_for(name):
@@ -42,15 +50,32 @@ def settings_for(name):
     if name == "tiny":
         return mvs.SystemSettings(array_width=aw, array_height=ah, min_disp=0, max_disp=16, inc=1, bl_ratio=1.0,
                                   kernel_size=128), W, H
+    if name == "bundled_15view_legacy":   # SURVEY 8(d) settings B (clMVDE.cpp:26-29 comments, photo_consistency.cpp:325-326)
+        return mvs.SystemSettings(array_width=aw, array_height=ah, min_disp=10, max_disp=100, inc=2, bl_ratio=0.625), W, H
     # shipped literals (clMVDE.cpp:14-36) with the array geometry of the workload
     return mvs.SystemSettings(array_width=aw, array_height=ah), W, H
+
+
+def data_kind(name):
+    return "bundled" if name in BUNDLED else "synthetic"
 
 
 def make_input(name, seed=0xC2):
     from cl_multiview_stereo_b200 import synth
     s, W, H = settings_for(name)
-    if name == "tiny":
+    if name in BUNDLED:
+        from cl_multiview_stereo_b200 import datasets
+        if not datasets.available(BUNDLED[name]):
+            raise SystemExit(f"workload {name}: the reference's images are not under tests/data/_ref "
+                             "(tests/data/fetch_bundled.py copies them where /root/reference exists)")
+        rgbx, aw, ah = datasets.load_set(BUNDLED[name])
+        assert (aw, ah) == (s.array_width, s.array_height) and rgbx.shape[1:3] == (H, W)
+    elif name == "tiny":
         rgbx, gt = synth.make_frame(7, W, H, s.array_width, s.array_height, 1.0, 5, 4, 14)
+    elif name == "noise_15view_1080p":
+        rng = np.random.default_rng(seed)
+        rgbx = rng.integers(0, 256, size=(s.array_width * s.array_height, H, W, 4), dtype=np.uint8)
+        rgbx[..., 3] = 0
     else:
         rgbx, gt = synth.make_frame(seed, W, H, s.array_width, s.array_height, s.bl_ratio, 12, 32.0, 58.0)
     return s, W, H, rgbx
@@ -120,137 +145,91 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------
-# CPU path (oracle port of the reference's OpenCL kernels), bounded sample, extrapolated to a frame
+# CPU path: WHOLE frames through the reference's own kernel source on the host cores (no sampling, no model)
 # ---------------------------------------------------------------------------------------------
 class CpuPath:
-    """Times the CPU restatement on a bounded sample of the workload.  Views are prepared once
-    (untimed) so that block matching / refinement have real neighbour data; each step then times
-      SLIC of one full view, boundary + flatness + init state + fusion of all views, and for one
-      interior and one corner view a slab of superpixel rows of block matching and of every
-      propagate iteration;
-    the slab timings are scaled to the frame with a linear model in the neighbour-view count."""
+    """One step = one whole frame, stage by stage as pipeline::exe_pipeline runs it (SLIC of every view, boundary,
+    block matching, flatness, init state, no_prop x propagate, spixl_to_image), every kernel from
+    oracle/_ref/libclref.so -- the reference's clcode.cl compiled as C++ over a work-item shim, OpenMP over
+    work-items -- where that library was built (kind "reference"); the C port of the same kernels otherwise
+    (kind "port").  One exception: update_cluster_center needs 256-work-item groups with barriers, which the
+    shim can only run as 256 real threads per group (minutes per launch at this size); its C port -- pinned bit
+    for bit to the reference kernel on small images, tests/test_cpu_reference_pin.py -- is timed in its place."""
 
     def __init__(self, name):
         from tests import orc, clref
         self.o = orc.load()
-        # the reference's own kernel source compiled for the CPU (oracle/_ref/libclref.so), when it was built
         self.r = clref.load() if clref.available() else None
         self.kind = "reference" if self.r is not None else "port"
+        self.name = name
         self.s, self.W, self.H, self.rgbx = make_input(name)
         s = self.s
         self.V = s.array_width * s.array_height
         self.levels = self.o.make_levels(s.min_disp, s.max_disp, s.inc)
         self.sub, self.num = self.o.make_subsets(s.array_width, s.array_height, s.neib_hor, s.neib_ver)
         self.cores = self.o.num_threads()
-        self.prepared = False
-
-    def prepare(self):
-        o, s = self.o, self.s
-        labs, maps, idxs = [], [], []
-        for v in range(self.V):
-            l, m, i = o.slic(self.rgbx[v], s.spixl_size, s.slic_color_weight, s.no_iter, s.enforce_connectivity)
-            labs.append(l); maps.append(m); idxs.append(i)
-        self.lab, self.map, self.idx = np.stack(labs), np.stack(maps), np.stack(idxs)
-        self.rep = o.boundary(self.map, self.idx, s.spixl_size)
-        # initial disparities of all views come from the slab runs below being too sparse, so take
-        # a cheap stand-in: every superpixel starts at the middle level (only timing depends on it)
-        self.map[..., 7] = self.levels[len(self.levels) // 2]
-        self.g_ = np.float32(2 * float(s.gamma) ** 2)
-        self.a_ = np.float32(2 * float(s.alpha) ** 2)
-        self.gam, self.alp, self.fus, self.kss = o.refine_params(self.g_, self.a_, s.fuse, s.kernel_step,
-                                                                 s.kernel_size // 2, s.spixl_size)
-        self.flat = o.flatness(self.map, np.float32(1.0 / float(self.g_)))
-        self.state = o.init_state(self.map, self.idx, self.rep, self.flat, self.sub, self.num, s.array_width, s.bl_ratio,
-                                  self.gam, self.alp, self.fus, s.kernel_step, self.kss)
-        self.scratch = np.zeros_like(self.state)
-        self.prepared = True
+        self.last = None
 
     def step(self, k=0):
-        """returns (extrapolated seconds per frame, per-stage seconds)"""
-        if not self.prepared:
-            self.prepare()
-        o, s, V = self.o, self.s, self.V
-        mh = self.map.shape[1]
-        rows = max(2, min(mh, 8))
-        y0 = (mh - rows) // 2
-        scale_rows = mh / rows
-        aw = s.array_width
-        zi = (s.array_height // 2) * aw + aw // 2      # interior view
-        zc = 0                                          # corner view
-        ni, nc = int(self.num[zi]), int(self.num[zc])
+        """-> (seconds of this frame, per-stage seconds); nothing is extrapolated"""
+        o, r, s, V = self.o, self.r, self.s, self.V
+        S, aw = s.spixl_size, s.array_width
         T = {}
-        r = self.r
-        S = s.spixl_size
+        t_frame = time.perf_counter()
         t = time.perf_counter()
-        if r is None:
-            o.slic(self.rgbx[k % V], S, s.slic_color_weight, s.no_iter, s.enforce_connectivity)
-        else:
-            # clSLIC::do_super_pixel_seg (clSLIC.cpp:67-122) kernel by kernel from the reference source; only the
-            # centre update runs the port (its 256-work-item barrier has no cheap CPU form)
-            mxy, mcol = o.slic_params(S)
-            lab = r.cvt(self.rgbx[k % V])
-            mp = r.init_centers(lab, S)
-            ix = r.assoc(lab, mp, S, s.slic_color_weight, mxy, mcol)
-            for _ in range(s.no_iter):
-                mp = o.update_centers(lab, ix, mp, S)
-                ix = r.assoc(lab, mp, S, s.slic_color_weight, mxy, mcol)
-            if s.enforce_connectivity:
-                ix = r.suppress(r.suppress(ix))
-        T["slic"] = (time.perf_counter() - t) * V
-        t = time.perf_counter()
-        (r or o).boundary(self.map, self.idx, S)
-        T["boundary"] = time.perf_counter() - t
-
-        def model(ti, tc):   # t(n) = a + b*n fitted on the interior / corner view, summed over the views
-            if ni == nc:
-                return ti * V
-            b = (ti - tc) / (ni - nc)
-            a = ti - b * ni
-            return float(sum(max(a + b * int(n), 0.0) for n in self.num))
-
-        def bm_rows(z):
+        labs, maps, idxs = [], [], []
+        mxy, mcol = o.slic_params(S)
+        for v in range(V):
             if r is None:
-                o.block_match_rows(self.lab, self.map, self.rep, self.levels, self.sub, self.num, aw, s.bl_ratio, z, y0, y0 + rows)
-            else:
-                r.block_match_rows(self.lab, self.map, self.rep, self.idx, self.levels, self.sub, self.num, aw, s.bl_ratio,
-                                   S, z, y0, y0 + rows)
-
+                lab, mp, ix = o.slic(self.rgbx[v], S, s.slic_color_weight, s.no_iter, s.enforce_connectivity)
+            else:   # clSLIC::do_super_pixel_seg (clSLIC.cpp:67-122) kernel by kernel
+                lab = r.cvt(self.rgbx[v])
+                mp = r.init_centers(lab, S)
+                ix = r.assoc(lab, mp, S, s.slic_color_weight, mxy, mcol)
+                for _ in range(s.no_iter):
+                    mp = o.update_centers(lab, ix, mp, S)
+                    ix = r.assoc(lab, mp, S, s.slic_color_weight, mxy, mcol)
+                if s.enforce_connectivity:
+                    ix = r.suppress(r.suppress(ix))
+            labs.append(lab); maps.append(mp); idxs.append(ix)
+        lab, mp, idx = np.stack(labs), np.stack(maps), np.stack(idxs)
+        del labs, maps, idxs
+        T["slic"] = time.perf_counter() - t
+        k_ = r or o
         t = time.perf_counter()
-        bm_rows(zi)
-        ti = time.perf_counter() - t
+        rep = k_.boundary(mp, idx, S)
+        T["boundary"] = time.perf_counter() - t
         t = time.perf_counter()
-        bm_rows(zc)
-        tc = time.perf_counter() - t
-        T["block_match"] = model(ti, tc) * scale_rows
+        mp = (r.block_match(lab, mp, rep, idx, self.levels, self.sub, self.num, aw, s.bl_ratio, S) if r is not None
+              else o.block_match(lab, mp, rep, self.levels, self.sub, self.num, aw, s.bl_ratio))
+        T["block_match"] = time.perf_counter() - t
+        g_, a_ = np.float32(2 * float(s.gamma) ** 2), np.float32(2 * float(s.alpha) ** 2)
+        gam, alp, fus, kss = o.refine_params(g_, a_, s.fuse, s.kernel_step, s.kernel_size // 2, S)
         t = time.perf_counter()
-        (r or o).flatness(self.map, np.float32(1.0 / float(self.g_)))
+        flat = k_.flatness(mp, np.float32(1.0 / float(g_)))
         T["flatness"] = time.perf_counter() - t
         t = time.perf_counter()
-        (r or o).init_state(self.map, self.idx, self.rep, self.flat, self.sub, self.num, aw, s.bl_ratio, self.gam, self.alp,
-                            self.fus, s.kernel_step, self.kss)
+        st = [k_.init_state(mp, idx, rep, flat, self.sub, self.num, aw, s.bl_ratio, gam, alp, fus, s.kernel_step, kss), None]
         T["init_state"] = time.perf_counter() - t
-        T["propagate"] = 0.0
-        for it in range(s.no_prop):
-            tt = []
-            for z in (zi, zc):
-                t = time.perf_counter()
-                (r or o).propagate_rows(self.state, self.scratch, self.map, self.idx, self.rep, self.flat, self.sub, self.num,
-                                        it, aw, s.bl_ratio, self.gam, self.alp, self.fus, s.kernel_step // (it + 1),
-                                        np.float32(self.kss) / np.float32(it + 1), z, y0, y0 + rows)
-                tt.append(time.perf_counter() - t)
-            T["propagate"] += model(tt[0], tt[1]) * scale_rows
         t = time.perf_counter()
-        (r or o).spixl_to_image(self.map, self.idx, self.state)
+        for it in range(s.no_prop):
+            src, dst = it % 2, 1 - it % 2
+            st[dst] = k_.propagate(st[src], mp, idx, rep, flat, self.sub, self.num, it, aw, s.bl_ratio, gam, alp, fus,
+                                   s.kernel_step // (it + 1), np.float32(kss) / np.float32(it + 1))
+        T["propagate"] = time.perf_counter() - t
+        t = time.perf_counter()
+        disp = k_.spixl_to_image(mp, idx, st[0])
         T["fusion"] = time.perf_counter() - t
-        return sum(T.values()), T
+        self.last = disp
+        return time.perf_counter() - t_frame, T
 
     def sample_desc(self):
         who = ("the reference's own kernel source (clcode.cl compiled as C++ over a work-item shim, oracle/_ref/libclref.so; "
-               "only update_cluster_center runs the C port)" if self.r is not None else "CPU oracle (port of clcode.cl)")
-        return (who + ", OpenMP over work-items: per step SLIC of 1 of %d views (x%d), boundary/flatness/"
-                "init_state/fusion of all views, and 8 of %d superpixel rows of block matching and of each of the %d "
-                "propagate iterations for one interior and one corner view, scaled by rows and by a linear model in "
-                "the neighbour-view count" % (self.V, self.V, self.map.shape[1], self.s.no_prop))
+               "update_cluster_center alone runs its bit-identical C port: the kernel needs 256-work-item barrier groups)"
+               if self.r is not None else "CPU oracle (C port of clcode.cl)")
+        return (who + ", OpenMP over work-items, on WHOLE frames of the workload: every stage, every view, every "
+                "superpixel (SLIC -> boundary -> block matching -> flatness -> init state -> %d x propagate -> "
+                "spixl_to_image); one step = one frame, measured, nothing sampled or extrapolated" % self.s.no_prop)
 
 
 def run_reference(args, rank, world):
@@ -260,30 +239,36 @@ def run_reference(args, rank, world):
     # host cores (the OpenMP runtime reads this when the oracle libraries are loaded, below)
     os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     cp = CpuPath(args.workload)
-    cp.prepare()
-    for k in range(args.warmup):
+    budget = float(os.environ.get("MVS_REF_BUDGET_S", "1500"))
+    t_all = time.perf_counter()
+    warm = min(args.warmup, 1)          # a CPU frame takes seconds: one untimed frame warms pages and the thread pool
+    for k in range(warm):
         cp.step(k)
-    t0 = time.perf_counter()
     secs = []
     stages = {}
     for k in range(args.steps):
         sec, T = cp.step(k)
         secs.append(sec)
         for a, b in T.items():
-            stages[a] = stages.get(a, 0.0) + b * 1e3 / args.steps
-    wall = time.perf_counter() - t0
+            stages[a] = stages.get(a, 0.0) + b * 1e3
+        # never extrapolate: if the wall budget would be overrun, stop and report the steps that were timed
+        if k + 1 < args.steps and (time.perf_counter() - t_all) + 1.5 * sec > budget:
+            break
+    done = len(secs)
     frame_s = float(np.mean(secs))
     value = 1.0 / frame_s
     s = cp.s
     line = {
         "impl": "reference", "metric": "15-view depth frames/s", "value": value, "unit": "frames/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": frame_s * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.workload, s, cp.W, cp.H),
+        "steps": done, "warmup": warm, "ms_per_step": frame_s * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": data_kind(args.workload),
+        "config": dict(workload_config(args.workload, s, cp.W, cp.H), parallelism=f"frame-parallel x{world}"),
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cp.cores, "kind": cp.kind,
                          "sample": cp.sample_desc()},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "stage_ms": stages, "sample_wall_s_per_step": wall / max(args.steps, 1), "gpu_launches": 0,
+        "stage_ms": {a: b / done for a, b in stages.items()},
+        "steps_asked": args.steps, "warmup_asked": args.warmup, "timed_wall_s": float(sum(secs)),
+        "ms_per_step_minmax": [min(secs) * 1e3, max(secs) * 1e3], "gpu_launches": 0,
     }
     emit(line)
 
@@ -320,6 +305,45 @@ def workload_config(name, s, W, H):
 # ---------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------
+def measure_resident(mvs, ctx, frame, steps, warmup, barrier=lambda: None):
+    """device-resident frames: (ms per frame by CUDA events around `steps` runs, launches per frame).  The timed
+    loop carries no per-stage events (mvs_frame_set_timing is off)."""
+    frame.set_timing(False)
+    for _ in range(warmup):
+        frame.run()
+    ctx.sync()
+    barrier()
+    l0 = ctx.launches
+    ctx.event_record(0)
+    for _ in range(steps):
+        frame.run()
+    ctx.event_record(1)
+    ctx.sync()
+    return ctx.event_elapsed_ms(0, 1) / steps, (ctx.launches - l0) / steps
+
+
+def stage_split(frame, steps):
+    """per-stage CUDA-event times, in a pass of its own"""
+    frame.set_timing(True)
+    frame.stage_ms()
+    for _ in range(steps):
+        frame.run()
+    st = {k: v / steps for k, v in frame.stage_ms().items()}
+    frame.set_timing(False)
+    return st
+
+
+def propagate_work(frame, s):
+    """candidate planes and bit-identical-unique planes per superpixel and iteration (one untimed diagnostic pass):
+    k_propagate evaluates only the unique ones, so its time depends on how diverse the scene's planes are"""
+    frame.slic(); frame.block_match(); frame.flatness(); frame.init_state()
+    st = [frame.propagate_stats(i) for i in range(s.no_prop)]
+    return {"candidates_per_superpixel": [round(x["candidates"] / max(x["superpixels"], 1), 2) for x in st],
+            "unique_planes_per_superpixel": [round(x["unique_planes"] / max(x["superpixels"], 1), 2) for x in st],
+            "plane_view_items": [x["items"] for x in st],
+            "samples_inside": [x["samples_inside"] for x in st]}
+
+
 def run_ours(args, rank, world, local_rank):
     dist = None
     if world > 1:
@@ -349,12 +373,12 @@ def run_ours(args, rank, world, local_rank):
     frame.upload(mvs.BUF_RGBX, rgbx)
 
     # ---- device-resident throughput (inputs already in HBM) -------------------------------
+    sampler = ClockSampler(local_rank)
+    frame.set_timing(False)
     for _ in range(args.warmup):
         frame.run()
     ctx.sync()
-    frame.stage_ms()                       # drop warm-up stage events
     barrier()
-    sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     l0 = ctx.launches
@@ -368,18 +392,15 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     ms_total = max_over_ranks(ms_total)
     clocks = sampler.stop() if rank == 0 else None
-    stage = frame.stage_ms()
-    stage = {k: v / args.steps for k, v in stage.items()}
     ms_step = ms_total / args.steps
     value = world * 1e3 / ms_step          # frames/s over all ranks (frame-parallel)
+    stage = stage_split(frame, min(args.steps, 5))
 
     # ---- end to end through the public API with HOST buffers ---------------------------------
     # two contexts/frames alternate so the copies of one frame overlap the kernels of the other
     ctx2 = mvs.Context(local_rank)
     frame2 = mvs.Frame(ctx2, s, W, H)
     ctxs, frames = [ctx, ctx2], [frame, frame2]
-    for f in frames:
-        f.set_timing(False)
     pin_in = mvs.PinnedBuffer(rgbx.shape, np.uint8)
     pin_in.array[...] = rgbx
     pin_out = [mvs.PinnedBuffer((V, H, W), np.float32) for _ in range(2)]
@@ -406,6 +427,8 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     frame2.close(); ctx2.close()
 
+    work = propagate_work(frame, s) if rank == 0 else None
+
     # ---- one frame sharded by view over all ranks (NCCL halo exchange) ----------------------------
     view_sharded = None
     if world > 1:
@@ -428,17 +451,21 @@ def run_ours(args, rank, world, local_rank):
                 fs.upload(mvs.BUF_RGBX, rgbx[lo:hi], lo, hi)
             for _ in range(args.warmup):
                 fs.run()
-            ctx.sync(); fs.stage_ms(); barrier()
+            ctx.sync(); barrier()
             ctx.event_record(4)
             for _ in range(args.steps):
                 fs.run()
             ctx.event_record(5)
             ctx.sync()
             vs_ms = max_over_ranks(ctx.event_elapsed_ms(4, 5)) / args.steps
-            st = fs.stage_ms()
+            barrier()
+            fs.set_timing(True); fs.stage_ms()
+            for _ in range(min(args.steps, 5)):
+                fs.run()
+            st = {k: v / min(args.steps, 5) for k, v in fs.stage_ms().items()}
+            fs.set_timing(False)
             # sharded result must equal the single-GPU result bit for bit on the views this rank owns
             same = True
-            fs.set_timing(False)
             fs.view_fusion()                   # every rank takes part in the exchange of the disparity images
             if hi > lo:
                 for which in (mvs.BUF_DISP, mvs.BUF_DISP_FUSED):
@@ -448,7 +475,7 @@ def run_ours(args, rank, world, local_rank):
             same = max_over_ranks(0.0 if same else 1.0) == 0.0
             runs[name] = {"value": 1e3 / vs_ms, "unit": "frames/s", "ms_per_step": vs_ms, "scaling": "strong",
                           "partition": name, "views_per_rank": [b - a for a, b in table],
-                          "exchange_ms_rank0": st["exchange"] / args.steps, "bit_identical_to_1gpu": same}
+                          "exchange_ms_rank0": st["exchange"], "stage_ms_rank0": st, "bit_identical_to_1gpu": same}
             fs.close()
             barrier()
         best = min(runs, key=lambda k: runs[k]["ms_per_step"])
@@ -472,36 +499,55 @@ def run_ours(args, rank, world, local_rank):
         # dominant kernel: propagate, one launch per iteration covering all views
         prop_bytes = sb["propagate"] / s.no_prop * V
         prop_ms = stage["propagate"] / s.no_prop
-        traffic = None
+        prof = {}
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("k_propagate")
+            prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
         except Exception:
             pass
         roofline = {"kernel": "k_propagate", "bound": "hbm", "achieved": prop_bytes / (prop_ms * 1e-3) / 1e9,
                     "peak": peak, "unit": "GB/s", "frac": prop_bytes / (prop_ms * 1e-3) / 1e9 / peak,
-                    "traffic": traffic, "peak_source": peak_src, "alg_bytes_per_launch": prop_bytes,
+                    "traffic": prof.get("k_propagate"), "peak_source": peak_src, "alg_bytes_per_launch": prop_bytes,
                     "avg_launch_ms": prop_ms,
-                    "note": "propagate is FP32-issue / dependent-gather bound (about 2e5 instructions per "
-                            "superpixel-iteration against 350 B of unique traffic), so its HBM fraction is tiny "
-                            "by construction; HBM-bound stages are listed in stage_hbm"}
+                    # what actually binds it (from the committed ncu capture, not from this run)
+                    "issue": prof.get("k_propagate_issue"),
+                    "note": "propagate is bound by instruction issue and dependent-gather latency (about 2e5 instructions "
+                            "per superpixel-iteration against 350 B of unique traffic), so its HBM fraction is tiny by "
+                            "construction; avg_launch_ms includes the k_pixel_plane pass that feeds it; HBM-bound "
+                            "stages are listed in stage_hbm"}
         cpu = None
         if world == 1 and not args.no_cpu:
             cp = CpuPath(args.workload)
             sec, T = cp.step(0)
             cpu = {"value": 1.0 / sec, "unit": "frames/s", "cores": cp.cores, "kind": cp.kind,
-                   "sample": cp.sample_desc(), "stage_ms": {k: v * 1e3 for k, v in T.items()}}
+                   "sample": cp.sample_desc() + "; here: one frame", "stage_ms": {k: v * 1e3 for k, v in T.items()}}
+        other = None
+        if world == 1 and not args.no_extra and args.workload == "15view_1080p":
+            other = {}
+            for name in ("bundled_15view", "noise_15view_1080p"):
+                try:
+                    s2, W2, H2, rgbx2 = make_input(name)
+                except SystemExit as e:
+                    other[name] = {"unavailable": str(e)}
+                    continue
+                f2 = mvs.Frame(ctx, s2, W2, H2)
+                f2.upload(mvs.BUF_RGBX, rgbx2)
+                ms2, _ = measure_resident(mvs, ctx, f2, max(3, args.steps // 2), 3)
+                st2 = stage_split(f2, 3)
+                other[name] = {"value": 1e3 / ms2, "unit": "frames/s", "ms_per_step": ms2, "data": data_kind(name),
+                               "stage_ms": st2, "propagate_work": propagate_work(f2, s2)}
+                f2.close()
         line = {
             "metric": "15-view depth frames/s", "value": value, "unit": "frames/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": data_kind(args.workload),
             "config": dict(workload_config(args.workload, s, W, H), parallelism=f"frame-parallel x{world}"),
             "clocks": clocks,
             "e2e": {"value": world * 1e3 / e2e_ms, "unit": "frames/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(rgbx.nbytes), "d2h_bytes_per_step": int(V * H * W * 4),
                     "result_checksum": checksum},
             "gpu_launches": int(launches),
-            "roofline": roofline, "stage_ms": stage, "stage_hbm": stage_hbm,
-            "cpu_baseline": cpu, "view_sharded": view_sharded,
+            "roofline": roofline, "stage_ms": stage, "stage_hbm": stage_hbm, "propagate_work": work,
+            "cpu_baseline": cpu, "view_sharded": view_sharded, "other_data": other,
         }
         emit(line)
     frame.close()
@@ -539,9 +585,10 @@ def run_slic_batch(args, rank, world, local_rank):
     ctx = mvs.Context(local_rank)
     frame = mvs.Frame(ctx, s, W, H)
     frame.upload(mvs.BUF_RGBX, imgs)
+    frame.set_timing(False)
     for _ in range(args.warmup):
         frame.slic()
-    ctx.sync(); frame.stage_ms()
+    ctx.sync()
     if dist is not None:
         dist.barrier()
     sampler = ClockSampler(local_rank)
@@ -626,6 +673,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="15view_1080p", choices=sorted(WORKLOADS) + ["slic_4k"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra lines on the bundled / noise frames (other_data)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

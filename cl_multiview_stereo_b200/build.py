@@ -118,6 +118,8 @@ def build_oracle(force=False):
     ref_mk = os.path.join(odir, "ref", "Makefile")
     if os.path.isdir("/root/reference/clMVDE") and os.path.exists(ref_mk):
         subprocess.check_call(["make", "-C", os.path.join(odir, "ref"), "-s"])
+        # the reference's HOST sources (CPU twins) over inert OpenCL / OpenCV headers: a timed baseline, not an oracle
+        subprocess.check_call(["make", "-C", os.path.join(odir, "ref_host"), "-s"])
     return os.path.join(odir, "liboracle.so")
 
 

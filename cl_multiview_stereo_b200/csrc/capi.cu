@@ -364,7 +364,7 @@ extern "C" int mvs_frame_destroy(mvs_frame *f)
     FrameDev &d = f->d;
     void *bufs[] = {d.rgbx, d.lab, d.idx, d.idx_tmp, d.map, d.rep, d.flat, d.disp, d.pixd, d.disp_proj, d.disp_fused,
                     d.io_stage, d.view_subset, d.subset_num, d.levels, d.plane[0], d.plane[1], d.cost[0], d.cost[1],
-                    d.state6[0], d.state6[1], d.edge, d.pixcol};
+                    d.state6[0], d.state6[1], d.edge, d.pixcol, d.spcol};
     for (void *p : bufs) if (p) keep(cudaFree(p));
     for (cudaEvent_t e : f->ev) keep(cudaEventDestroy(e));
     delete f;
@@ -851,6 +851,10 @@ static int propagate_impl(mvs_frame *f, int iter, unsigned long long *stats_dev)
     // per-pixel {label, input-plane disparity} of every view this rank's superpixels project into
     std::vector<std::pair<int, int>> runs;
     read_view_runs(f, runs);
+    if (iter == 0 || !f->d.spcol) {   // superpixel colours as 16-byte records (fixed from SLIC on)
+        if (!f->d.spcol) CK(cudaMalloc(&f->d.spcol, sizeof(float4) * (size_t)f->d.V * f->d.M));
+        for (auto &r : runs) f->ctx->launches += launch_spixl_colour(f->d, r.first, r.second, f->ctx->stream);
+    }
     if (propagate_needs() == 2 && (iter == 0 || !f->d.pixcol)) {   // colours are fixed from block matching on
         if (!f->d.pixcol) CK(cudaMalloc(&f->d.pixcol, sizeof(float4) * (size_t)f->d.V * f->d.N));
         for (auto &r : runs) f->ctx->launches += launch_pixel_colour(f->d, r.first, r.second, f->ctx->stream);

@@ -25,6 +25,7 @@ struct FrameDev {
                         //          walk gathers per sample (rebuilt before every iteration; allocated on demand)
     float *disp_proj;   // [V][N]   multi-view fusion: chased disparity (allocated on demand)
     float *disp_fused;  // [V][N]   multi-view fusion: voted disparity (allocated on demand)
+    float4 *spcol;      // [V][M]   {L, a, b, 0} per superpixel, packed from map after block matching (allocated on demand)
     float4 *pixcol;     // [V][N]   {L, a, b, 0} of the pixel's superpixel (only when propagate_needs() == 2; on demand)
     float *edge;        // [V][N]   edge-aware SLIC: Sobel magnitude of Lab (edge_enable; allocated on demand)
     uint8_t *io_stage;  // [V][N][4] staging of packed BGR input / 8-bit and overlay output (allocated on demand)
@@ -64,6 +65,7 @@ int launch_propagate(const FrameDev &f, const RefineArgs &a, int src, int dst, i
                      unsigned long long *stats = nullptr);
 int launch_spixl_to_image(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);
 int launch_pixel_plane(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);
+int launch_spixl_colour(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int launch_pixel_colour(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int propagate_needs();
 int launch_view_fusion(const FrameDev &f, float bl_ratio, float fuse, int z0, int z1, cudaStream_t st);

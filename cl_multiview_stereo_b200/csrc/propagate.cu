@@ -65,6 +65,8 @@ struct PArgs {
     const int *view_subset, *subset_num;
     const uint2 *pixd;        // [V][N] {label, input-plane disparity at the pixel} (k_pixel_plane)
     const float4 *pixcol;     // [V][N] {L, a, b, 0} of the pixel's superpixel (k_pixel_colour; PR_COL 2)
+    const float4 *spcol;      // [V][M] {L, a, b, 0} of every superpixel: half the bytes and half the cache lines of the
+                              //        32-byte centre records for the colour gather of the consistency walk (PR_COL 0)
     const float4 *plane_in;   // [V][M] {d,nx,ny,nz}
     const float2 *cost_in;    // [V][M] {sm,cs}
     float4 *plane_out;
@@ -386,9 +388,9 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
 #pragma unroll
                         for (int j = 0; j < 3; ++j) col[j] = __ldg(a.pixcol + nbase + (uint32_t)pix[j]);
 #elif PR_COL == 0
-                        Rec8 rec[3];
+                        float4 col[3];
 #pragma unroll
-                        for (int j = 0; j < 3; ++j) rec[j] = ld_rec8(a.map + 2 * (mbase + pr[j].x));
+                        for (int j = 0; j < 3; ++j) col[j] = __ldg(a.spcol + mbase + pr[j].x);
 #endif
 #pragma unroll
                         for (int j = 0; j < 3; ++j)
@@ -404,7 +406,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                                 }
 #elif PR_COL == 0
                                 {
-                                    const float cdiff = dist3(rec[j].L, rec[j].a, rec[j].b, cL, ca, cb);
+                                    const float cdiff = dist3(col[j].x, col[j].y, col[j].z, cL, ca, cb);
                                     sim = expf_pinned<NP>(-cdiff * cdiff * a.gamma);
                                 }
 #else
@@ -644,7 +646,7 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     PArgs a;
     a.map = f.map; a.idx = f.idx; a.rep = f.rep; a.flat = f.flat;
     a.view_subset = f.view_subset; a.subset_num = f.subset_num;
-    a.pixd = f.pixd; a.pixcol = f.pixcol;
+    a.pixd = f.pixd; a.pixcol = f.pixcol; a.spcol = f.spcol;
     a.plane_in = f.plane[src]; a.cost_in = f.cost[src]; a.plane_out = f.plane[dst]; a.cost_out = f.cost[dst];
     a.V = f.V; a.W = f.W; a.H = f.H; a.mw = f.mw; a.mh = f.mh; a.N = f.N; a.M = f.M; a.aw = f.aw;
     a.gamma = r.gamma; a.alpha = r.alpha; a.bl_ratio = r.bl_ratio; a.fuse = r.fuse;
@@ -680,7 +682,7 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     const bool np = a.gamma >= 0.0f && a.alpha >= 0.0f;
     // the per-pixel record path needs f.pixd (k_pixel_plane of the SAME input state) and view slots below 255
     static const bool legacy = [] { const char *e = getenv("MVS_PROP_MODE"); return e && !strcmp(e, "legacy"); }();
-    const bool pixd = !legacy && f.pixd && a.nsmax < 255 && (PR_COL != 2 || f.pixcol);
+    const bool pixd = !legacy && f.pixd && a.nsmax < 255 && (PR_COL != 2 || f.pixcol) && (PR_COL != 0 || f.spcol);
 #define PR_LAUNCH(U, B, P, X, S)                                                                                 \
     do {                                                                                                         \
         if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B, P, X, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \

@@ -319,6 +319,23 @@ __global__ void __launch_bounds__(256) k_pixel_plane4(const float4 *__restrict__
     pixd4[2 * pq + 1] = make_uint4(q[2], o[2], q[3], o[3]);
 }
 
+// {L, a, b, 0} of every superpixel as one 16-byte record (the colours are fixed once SLIC is done)
+__global__ void __launch_bounds__(256) k_spixl_colour(const float4 *__restrict__ map, float4 *__restrict__ spcol, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = map[2 * i], b = map[2 * i + 1];
+    spcol[i] = make_float4(a.w, b.x, b.y, 0.0f);
+}
+
+int launch_spixl_colour(const FrameDev &f, int z0, int z1, cudaStream_t st)
+{
+    size_t n = (size_t)(z1 - z0) * f.M, o = (size_t)z0 * f.M;
+    if (!n) return 0;
+    k_spixl_colour<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(f.map + 2 * o, f.spcol + o, n);
+    return 1;
+}
+
 // per-pixel colour of the pixel's superpixel (constant over the refinement; an experiment knob of k_propagate)
 __global__ void __launch_bounds__(256) k_pixel_colour(const float4 *__restrict__ map, const uint32_t *__restrict__ idx,
                                                       float4 *__restrict__ pixcol, int W, int H, int N, int M, int z0)

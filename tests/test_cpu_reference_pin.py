@@ -151,3 +151,30 @@ def test_restatement_reproduces_view_fusion_golden(oracle, path):
     proj, fused = oracle.view_fusion(g["disp"], int(g["array_width"]), float(g["bl_ratio"]), float(g["fuse"]))
     assert_same(proj, g["proj"], "disp_proj")
     assert_same(fused, g["fused"], "fused disparity")
+
+
+def test_reference_host_twins_build_and_run():
+    """the reference's CPU twins (*_host methods) compile unmodified over the inert headers of oracle/ref_host and
+    run on a small frame; where a twin computes what the kernel computes (flatness: the same terms, N before S) it
+    agrees to the tolerance of the reference's own compare_host_to_device_flatness (1e-4, depth_refinement.cpp:209)"""
+    from tests import hosttwin, orc
+    if not hosttwin.available():
+        pytest.skip("no /root/reference and no prebuilt oracle/_ref/libhosttwin.so")
+    h = hosttwin.load()
+    o = orc.load()
+    import cl_multiview_stereo_b200 as mvs
+    from cl_multiview_stereo_b200 import synth
+    s = mvs.SystemSettings(array_width=5, array_height=3, min_disp=0, max_disp=16, inc=1, bl_ratio=0.625, kernel_size=128)
+    rgbx, _ = synth.make_frame(7, 96, 64, 5, 3, bl_ratio=0.625, n_patches=4, dmin=4, dmax=14)
+    ref = o.pipeline(rgbx, s)
+    sub, num = o.make_subsets(5, 3)
+    levels = o.make_levels(0, 16, 1)
+    mp, rep, sec = h.block_match(ref["lab"], ref["map_slic"], ref["idx"], levels, sub, num, 5, 0.625, 8)
+    assert np.isin(mp[..., 7], levels).all()
+    # array_width = 5 and bl_ratio = 0.625 are what the twin hard-codes (photo_consistency.cpp:325-326): on this
+    # geometry it mostly lands on the kernel's level (it has no centre clamp and truncates its steps, H3-H5)
+    assert (mp[..., 7] == ref["map"][..., 7]).mean() > 0.5
+    flat, sa, sb, t = h.refine(ref["map"], ref["idx"], ref["rep"], ref["lab"], 5, 3, 8, 0.625, sub, num, np.float32(8), np.float32(72),
+                               1.0, 13, 64, 3)
+    assert np.abs(flat - ref["flat"]).max() < 1e-4
+    assert np.isfinite(sa[..., :3]).all() and (sa[..., 5] != 0).any()
