@@ -45,12 +45,11 @@ class SystemSettings:
     no_prop: int = 5
 
     def params(self, width, height):
-        if self.edge_enable:
-            raise MvsError("edge_enable is not implemented (off at the reference's shipped settings)")
         return Params(width, height, self.spixl_size, self.array_width, self.array_height,
                       self.slic_color_weight, self.no_iter, int(self.enforce_connectivity),
                       self.neib_hor, self.neib_ver, self.min_disp, self.max_disp, self.inc, self.bl_ratio,
-                      self.kernel_size, self.kernel_step, self.fuse, self.gamma, self.alpha, self.no_prop)
+                      self.kernel_size, self.kernel_step, self.fuse, self.gamma, self.alpha, self.no_prop,
+                      int(self.edge_enable))
 
 
 def map_size(width, height, S):
@@ -335,6 +334,18 @@ class Frame:
     def exchange(self, which):
         check(lib().mvs_frame_exchange(self._h, which))
 
+    def halo_views(self):
+        """views this rank's own views read but the rank does not own (needs the communicator to be set up)"""
+        n = C.c_int()
+        check(lib().mvs_frame_halo_views(self._h, None, 0, C.byref(n)))
+        v = np.zeros(max(n.value, 1), np.int32)
+        check(lib().mvs_frame_halo_views(self._h, _ptr(v), n.value, C.byref(n)))
+        return [int(x) for x in v[:n.value]]
+
+    def set_halo_inputs(self, local=True):
+        """the caller uploads the halo views' input images itself (no image exchange between ranks)"""
+        check(lib().mvs_frame_set_halo_inputs(self._h, int(bool(local))))
+
     def set_timing(self, on):
         check(lib().mvs_frame_set_timing(self._h, int(bool(on))))
 
@@ -345,8 +356,8 @@ class Frame:
 
 
 # ---- class-level entry points with host arrays (the reference's per-stage semantics) ----
-def slic_run(ctx, rgbx, S=8, weight=0.6, no_iter=5, enforce_connectivity=False):
-    """clSLIC::do_super_pixel_seg for a batch rgbx[count,H,W,4] -> (lab, map, idx)"""
+def slic_run(ctx, rgbx, S=8, weight=0.6, no_iter=5, enforce_connectivity=False, edge_enable=False, want_edge=False):
+    """clSLIC::do_super_pixel_seg for a batch rgbx[count,H,W,4] -> (lab, map, idx) [+ edge image with want_edge]"""
     rgbx = np.ascontiguousarray(rgbx, dtype=np.uint8)
     if rgbx.ndim == 3:
         rgbx = rgbx[None]
@@ -355,8 +366,11 @@ def slic_run(ctx, rgbx, S=8, weight=0.6, no_iter=5, enforce_connectivity=False):
     lab = np.empty((cnt, H, W, 4), np.float32)
     mp = np.empty((cnt, mh, mw, 8), np.float32)
     idx = np.empty((cnt, H, W), np.uint32)
-    check(lib().mvs_slic_run(ctx._h, W, H, S, C.c_float(weight), no_iter, int(enforce_connectivity), cnt,
-                             _ptr(rgbx), _ptr(lab), _ptr(mp), _ptr(idx)))
+    edge = np.empty((cnt, H, W), np.float32) if want_edge else None
+    check(lib().mvs_slic_run_edge(ctx._h, W, H, S, C.c_float(weight), no_iter, int(enforce_connectivity), int(edge_enable),
+                                  cnt, _ptr(rgbx), _ptr(lab), _ptr(mp), _ptr(idx), _ptr(edge) if want_edge else None))
+    if want_edge:
+        return lab, mp, idx, edge
     return lab, mp, idx
 
 

@@ -112,6 +112,8 @@ struct mvs_frame {
     size_t ev_used = 0;
     bool timing = false;           // per-stage CUDA events are opt-in (mvs_frame_set_timing)
     std::string timer_err;         // first failure of an event call inside a StageTimer
+    bool halo_inputs_local = false;   // the caller uploads the halo views' input images (mvs_frame_set_halo_inputs)
+    bool halo_plane0 = false;      // plane[0] of the halo views already holds the initial state (mvs_frame_init_state)
 };
 
 extern "C" const char *mvs_last_error(void) { return g_err.c_str(); }
@@ -367,6 +369,8 @@ extern "C" int mvs_frame_destroy(mvs_frame *f)
                     d.state6[0], d.state6[1], d.edge, d.pixcol, d.spcol};
     for (void *p : bufs) if (p) keep(cudaFree(p));
     for (cudaEvent_t e : f->ev) keep(cudaEventDestroy(e));
+    delete d.bm_tma;
+    delete d.slic_tma;
     delete f;
     if (first != cudaSuccess) return fail("mvs_frame_destroy: %s", cudaGetErrorString(first));
     return 0;
@@ -387,7 +391,11 @@ static int frame_alloc(mvs_ctx *ctx, int W, int H, int S, int aw, int ah, bool n
     d.mw = (int)ceilf((float)W / (float)S);   // pipeline.cpp:18-19
     d.mh = (int)ceilf((float)H / (float)S);
     d.N = W * H; d.M = d.mw * d.mh;
-    if ((double)d.M >= 16777216.0) { delete f; return fail("more than 2^24 superpixels per view"); }
+    d.bm_tma = new BmTma();
+    d.bm_tma->state = 0;
+    d.slic_tma = new SlicTma();
+    d.slic_tma->state = 0;
+    if ((double)d.M >= 16777216.0) { delete d.bm_tma; delete d.slic_tma; delete f; return fail("more than 2^24 superpixels per view"); }
     size_t VN = (size_t)d.V * d.N, VM = (size_t)d.V * d.M;
     cudaError_t e = cudaSuccess;
     size_t asked = 0;
@@ -487,7 +495,8 @@ static int xfer(mvs_frame *f, int which, int v0, int v1, void *host, bool up, bo
     if (!up && state) f->ctx->launches += launch_export_state(f->d, w, v0, v1, st);
     if (up) CK(cudaMemcpyAsync(dev + per_view * v0, host, per_view * (v1 - v0), cudaMemcpyHostToDevice, st));
     else CK(cudaMemcpyAsync(host, dev + per_view * v0, per_view * (v1 - v0), cudaMemcpyDeviceToHost, st));
-    if (up && state) f->ctx->launches += launch_import_state(f->d, w, v0, v1, st);
+    if (up && state) { f->ctx->launches += launch_import_state(f->d, w, v0, v1, st); f->halo_plane0 = false; }
+    if (up && which == MVS_BUF_MAP) f->halo_plane0 = false;
     if (sync) CK(cudaStreamSynchronize(st));
     return 0;
 }
@@ -754,8 +763,16 @@ extern "C" int mvs_frame_slic(mvs_frame *f)
     a.max_color_dist *= a.max_color_dist;
     a.weight = f->p.slic_color_weight;
     long long &L = f->ctx->launches;
+    {
+        const char *why = "";
+        if (prepare_update_centers_tma(f->d, &why)) return fail("slic: tensor map: %s", why);
+    }
     L += launch_cvt(f->d, f->lo, f->hi, st);
     L += launch_init_centers(f->d, f->lo, f->hi, st);
+    if (f->p.edge_enable) {   // clSLIC.cpp:86
+        if (!f->d.edge) CK(cudaMalloc(&f->d.edge, sizeof(float) * (size_t)f->d.V * f->d.N));
+        L += launch_apply_edge_values(f->d, f->lo, f->hi, st);
+    }
     L += launch_assoc(f->d, a, f->lo, f->hi, st);
     for (int i = 0; i < f->p.no_iter; ++i) {
         L += launch_update_centers(f->d, f->lo, f->hi, st);
@@ -768,21 +785,57 @@ extern "C" int mvs_frame_slic(mvs_frame *f)
     return check_stage(f, "slic");
 }
 
-// after SLIC on a sharded frame: ship RGBX (4 B/px) + labels + centres of the halo views and
-// recompute their Lab locally (bit-identical by construction, 4x less traffic than Lab)
-static int exchange_after_slic(mvs_frame *f)
+// Sharded frame, halo data flow.  Block matching of a rank's own views reads only the Lab of their neighbour views;
+// labels and centres of the neighbours are first read by the refinement.  So:
+//   * the INPUT images of the halo views arrive first -- uploaded by the caller like the rank's own images
+//     (mvs_frame_set_halo_inputs; no transfer between ranks at all) or, failing that, sent by their owners in one
+//     NCCL group before anything is computed -- and the rank converts them to Lab itself (4 B/px instead of 16 B/px,
+//     the same bits by construction);
+//   * ONE group after block matching carries labels and centres (initial disparity included) of the halo views.
+static int halo_inputs(mvs_frame *f)
 {
     if (!f->ctx->comm || f->ctx->nranks == 1) return 0;
     CK(cudaSetDevice(f->ctx->device));
     StageTimer t(f, ST_EXCH);
-    // image, labels and centres of the halo views in one group (three groups cost two more waits on the neighbours)
-    char *base[3] = {(char *)f->d.rgbx, (char *)f->d.idx, (char *)f->d.map};
-    const size_t per_view[3] = {sizeof(uchar4) * (size_t)f->d.N, sizeof(uint32_t) * (size_t)f->d.N, 32 * (size_t)f->d.M};
-    if (exchange_raw_multi(f, 3, base, per_view)) return 1;
+    if (!f->halo_inputs_local)
+        if (exchange_raw(f, (char *)f->d.rgbx, sizeof(uchar4) * (size_t)f->d.N)) return 1;
     std::vector<int> halo;
     halo_views(f, halo);
     for (int v : halo) f->ctx->launches += launch_cvt(f->d, v, v + 1, f->ctx->stream);
     return check_launch("halo cvt");
+}
+
+static int exchange_after_block_match(mvs_frame *f)
+{
+    if (!f->ctx->comm || f->ctx->nranks == 1) return 0;
+    CK(cudaSetDevice(f->ctx->device));
+    StageTimer t(f, ST_EXCH);
+    char *base[2] = {(char *)f->d.idx, (char *)f->d.map};
+    const size_t per_view[2] = {sizeof(uint32_t) * (size_t)f->d.N, 32 * (size_t)f->d.M};
+    return exchange_raw_multi(f, 2, base, per_view);
+}
+
+// The caller uploads the input images of the halo views itself (every view this rank's views read: the camera images
+// are host data, a rank can ingest its neighbours' as well as its own), so no image crosses between ranks.
+extern "C" int mvs_frame_set_halo_inputs(mvs_frame *f, int local)
+{
+    if (!f) return fail("null frame");
+    f->halo_inputs_local = local != 0;
+    return 0;
+}
+
+// views this rank reads but does not own: count, and the view numbers when `views` has room
+extern "C" int mvs_frame_halo_views(mvs_frame *f, int *views, int cap, int *count)
+{
+    if (!f || !count) return fail("null argument");
+    std::vector<int> halo;
+    halo_views(f, halo);
+    *count = (int)halo.size();
+    if (views) {
+        if (cap < *count) return fail("mvs_frame_halo_views: %d views, room for %d", *count, cap);
+        for (int i = 0; i < *count; ++i) views[i] = halo[i];
+    }
+    return 0;
 }
 
 extern "C" int mvs_frame_block_match(mvs_frame *f)
@@ -796,6 +849,9 @@ extern "C" int mvs_frame_block_match(mvs_frame *f)
         f->ctx->launches += launch_boundary(f->d, f->lo, f->hi, st);
     }
     {
+        const char *why = "";
+        if (prepare_block_match_tma(f->d, f->h_levels.data(), (int)f->h_levels.size(), f->bl_ratio, &why))
+            return fail("block_match: tensor map: %s", why);
         StageTimer t(f, ST_BM);
         f->ctx->launches += launch_block_match(f->d, f->bl_ratio, f->lo, f->hi, st);
     }
@@ -818,6 +874,14 @@ extern "C" int mvs_frame_init_state(mvs_frame *f)
     StageTimer t(f, ST_INIT);
     RefineArgs a{f->gamma, f->alpha, f->fuse, f->bl_ratio, f->kernel_step, f->kss, 0};
     f->ctx->launches += launch_init_state(f->d, a, f->lo, f->hi, f->ctx->stream);
+    if (f->ctx->comm && f->ctx->nranks > 1) {
+        // the initial planes of the halo views follow from the centres this rank holds since the exchange after block
+        // matching: iteration 0 needs no plane exchange
+        std::vector<int> halo;
+        halo_views(f, halo);
+        for (int v : halo) f->ctx->launches += launch_plane_from_map(f->d, v, v + 1, f->ctx->stream);
+        f->halo_plane0 = true;
+    }
     return check_stage(f, "init_state");
 }
 
@@ -844,7 +908,9 @@ static int propagate_impl(mvs_frame *f, int iter, unsigned long long *stats_dev)
     if (iter < 0) return fail("negative iteration");
     CK(cudaSetDevice(f->ctx->device));
     int src = iter & 1, dst = src ^ 1;   // even: A -> B, odd: B -> A (depth_refinement.cpp:744-753)
-    if (f->ctx->comm && f->ctx->nranks > 1)
+    const bool have_halo = iter == 0 && f->halo_plane0;
+    f->halo_plane0 = false;
+    if (f->ctx->comm && f->ctx->nranks > 1 && !have_halo)
         if (mvs_frame_exchange(f, src ? MVS_BUF_STATE_B : MVS_BUF_STATE_A)) return 1;
     if (!f->d.pixd) CK(cudaMalloc(&f->d.pixd, sizeof(uint2) * (size_t)f->d.V * f->d.N));
     StageTimer t(f, ST_PROP);
@@ -969,11 +1035,10 @@ extern "C" int mvs_frame_refine(mvs_frame *f)
 
 extern "C" int mvs_frame_run(mvs_frame *f)
 {
+    if (halo_inputs(f)) return 1;
     if (mvs_frame_slic(f)) return 1;
-    if (exchange_after_slic(f)) return 1;
     if (mvs_frame_block_match(f)) return 1;
-    if (f->ctx->comm && f->ctx->nranks > 1)
-        if (mvs_frame_exchange(f, MVS_BUF_MAP)) return 1;
+    if (exchange_after_block_match(f)) return 1;
     return mvs_frame_refine(f);
 }
 
@@ -1060,24 +1125,39 @@ extern "C" int mvs_frame_draw_segmentation(mvs_frame *f, int v0, int v1, uint8_t
 // ---------------------------------------------------------------------------------------
 // class-level entry points (host pointers, reference semantics)
 // ---------------------------------------------------------------------------------------
-extern "C" int mvs_slic_run(mvs_ctx *ctx, int width, int height, int spixl_size, float color_weight, int no_iter,
-                            int enforce_connectivity, int count, const void *rgbx, void *lab, void *map, uint32_t *idx)
+extern "C" int mvs_slic_run_edge(mvs_ctx *ctx, int width, int height, int spixl_size, float color_weight, int no_iter,
+                                 int enforce_connectivity, int edge_enable, int count, const void *rgbx, void *lab,
+                                 void *map, uint32_t *idx, float *edge)
 {
     if (!rgbx) return fail("null input image");
     if (count <= 0) return fail("count must be positive");
+    if (edge && !edge_enable) return fail("an edge image was asked for with edge_enable off");
     mvs_frame *f = nullptr;
     // `count` independent images = a count x 1 "array" with no neighbour relations
     if (frame_alloc(ctx, width, height, spixl_size, count, 1, true, true, false, enforce_connectivity != 0, &f)) return 1;
     f->p.slic_color_weight = color_weight;
     f->p.no_iter = no_iter;
     f->p.enforce_connectivity = enforce_connectivity;
+    f->p.edge_enable = edge_enable;
     f->timing = false;
     int rc = mvs_frame_upload_async(f, MVS_BUF_RGBX, 0, count, rgbx) || mvs_frame_slic(f) ||
              (lab && mvs_frame_download_async(f, MVS_BUF_LAB, 0, count, lab)) ||
              (map && mvs_frame_download_async(f, MVS_BUF_MAP, 0, count, map)) ||
-             (idx && mvs_frame_download_async(f, MVS_BUF_IDX, 0, count, idx)) || mvs_ctx_sync(ctx);
+             (idx && mvs_frame_download_async(f, MVS_BUF_IDX, 0, count, idx));
+    if (!rc && edge) {
+        cudaError_t e = cudaMemcpyAsync(edge, f->d.edge, sizeof(float) * (size_t)count * f->d.N, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e != cudaSuccess) rc = fail("edge image download: %s", cudaGetErrorString(e));
+    }
+    rc = rc || mvs_ctx_sync(ctx);
     mvs_frame_destroy(f);
     return rc;
+}
+
+extern "C" int mvs_slic_run(mvs_ctx *ctx, int width, int height, int spixl_size, float color_weight, int no_iter,
+                            int enforce_connectivity, int count, const void *rgbx, void *lab, void *map, uint32_t *idx)
+{
+    return mvs_slic_run_edge(ctx, width, height, spixl_size, color_weight, no_iter, enforce_connectivity, 0, count, rgbx, lab,
+                             map, idx, nullptr);
 }
 
 // clSLIC::draw_segmentation_lines (clSLIC.cpp:447-478) with host arrays: `count` images + their labels in, the

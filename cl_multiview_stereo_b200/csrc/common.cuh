@@ -1,9 +1,29 @@
 // common.cuh -- shared declarations of the sm_100a depth-pipeline library.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace mvs {
+
+// Host-side cache of the block matcher's tensor maps (TMA boxes over the frame's Lab stack), one per geometric class
+// of a neighbour view: same camera row (0), same camera column (1), diagonal (2).  Rebuilt when the frame's Lab
+// pointer, the disparity range or bl_ratio change.  state: 0 = not built, 1 = ready, -1 = this geometry does not fit.
+struct BmTma {
+    CUtensorMap map[3];
+    int bw[3], bh[3];
+    const void *lab;
+    float dmin, dmax, bl_ratio;
+    int nlev;
+    int state;
+};
+
+// the same for the centre update of SLIC (S = 8): box loads of the Lab tile and the label tile of a CTA
+struct SlicTma {
+    CUtensorMap map_lab, map_idx;
+    const void *lab, *idx;
+    int state;
+};
 
 // Geometry + device pointers of one frame (all V views; view-major arrays).
 struct FrameDev {
@@ -33,6 +53,8 @@ struct FrameDev {
     int *subset_num;    // [V]
     float *levels;      // [L]
     int num_levels;
+    BmTma *bm_tma;      // host pointer (owned by the frame): tensor maps of the block matcher
+    SlicTma *slic_tma;  // host pointer (owned by the frame): tensor maps of the centre update
     int unit_baseline;  // every neighbour view at most one camera apart in x and y
     int max_neighbours; // largest subset_num over the views
 };
@@ -52,15 +74,19 @@ struct RefineArgs {
 // number of kernel launches it issued.
 int launch_cvt(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int launch_init_centers(const FrameDev &f, int z0, int z1, cudaStream_t st);
+int launch_apply_edge_values(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int launch_assoc(const FrameDev &f, const SlicArgs &a, int z0, int z1, cudaStream_t st);
 int launch_update_centers(const FrameDev &f, int z0, int z1, cudaStream_t st);
+int prepare_update_centers_tma(const FrameDev &f, const char **why);
 int launch_connectivity(const FrameDev &f, int z0, int z1, cudaStream_t st);
 
 int launch_boundary(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int launch_block_match(const FrameDev &f, float bl_ratio, int z0, int z1, cudaStream_t st);
+int prepare_block_match_tma(const FrameDev &f, const float *levels_host, int nlev, float bl_ratio, const char **why);
 
 int launch_flatness(const FrameDev &f, float gamma_flat, int z0, int z1, cudaStream_t st);
 int launch_init_state(const FrameDev &f, const RefineArgs &a, int z0, int z1, cudaStream_t st);
+int launch_plane_from_map(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int launch_propagate(const FrameDev &f, const RefineArgs &a, int src, int dst, int z0, int z1, cudaStream_t st,
                      unsigned long long *stats = nullptr);
 int launch_spixl_to_image(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);

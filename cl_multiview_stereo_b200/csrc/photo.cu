@@ -6,7 +6,11 @@
 // launches the matcher once per view; here every view is covered by one launch.
 #include "common.cuh"
 #include "mvs_math.cuh"
+#include "tma.cuh"
 #include <algorithm>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
 
 namespace mvs {
 
@@ -195,9 +199,247 @@ k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const ui
     if (lane == 0) reinterpret_cast<float *>(map + 2 * mi + 1)[3] = disp_est;
 }
 
+// ---------------------------------------------------------------------------------------
+// Block matching out of TMA-staged windows.
+//
+// The gather kernel above pushes every one of its 1.9e9 sixteen-byte samples per frame through the L1 tag stage
+// (L1 97 % busy, 33 % hits).  Here a CTA owns a TILE of BT_W x BT_H adjacent superpixels of one view.  For one
+// neighbour view at a time, everything the tile can sample there -- the bounding box of its reference samples,
+// displaced by the whole disparity range along the camera offset -- is a dense box of that view's Lab image: ONE
+// cp.async.bulk.tensor box load (TMA) brings it into shared memory, completion on an mbarrier, and the (level,
+// sample) loops of clcode.cl:1030-1053 then read shared memory with lanes = disparity levels.  The box width is
+// odd for a neighbour in the same camera column and even for a diagonal one, so that the 16-byte reads of the
+// eight lanes of a quarter-warp -- one image row apart, or one row and one column -- fall on distinct bank groups.
+// A sample that lands outside the staged box (a centre that has drifted unusually far) takes the global load.
+// The cost chain ('+30, -30', x outer / y inner), the minimum over views and the argmin over levels are those of
+// the kernel above; results are bit-identical.
+// ---------------------------------------------------------------------------------------
+constexpr int BT_W = 8, BT_H = 4;            // tile in superpixels
+constexpr int BT_SP = BT_W * BT_H;
+constexpr int BT_WARPS = 16;                 // two superpixels per warp
+static_assert(BT_SP == 2 * BT_WARPS, "two superpixels per warp");
+
+struct BmTmaArgs {
+    const float4 *lab;
+    float4 *map;
+    const uint2 *rep;
+    const float *levels;
+    const int *view_subset, *subset_num;
+    int disp_num, aw, V, W, H, N, M, mw, mh, z0;
+    float bl_ratio, dmin, dmax;
+    int bw[3], bh[3];
+};
+
+__global__ void __launch_bounds__(BT_WARPS * 32, 1)
+k_block_match_tma(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ CUtensorMap tm_col,
+                  const __grid_constant__ CUtensorMap tm_diag, const BmTmaArgs a)
+{
+    extern __shared__ __align__(128) unsigned char bt_smem[];
+    __shared__ float4 s_ref[BT_SP][25];
+    __shared__ float2 s_xy[BT_SP][25];
+    __shared__ int s_box[4];                 // xmin, xmax, ymin, ymax of the tile's reference samples
+    __shared__ __align__(8) uint64_t s_bar;
+    float4 *win = reinterpret_cast<float4 *>(bt_smem);
+    const unsigned FULL = 0xffffffffu;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // grid = (tile columns, views, tile rows): the views of one band of rows run together (L2 reuse of the rows a
+    // band reads from its neighbour views)
+    const int z = a.z0 + blockIdx.y;
+    if (threadIdx.x == 0) {
+        s_box[0] = 0x7fffffff; s_box[1] = -0x7fffffff; s_box[2] = 0x7fffffff; s_box[3] = -0x7fffffff;
+        mbar_init(&s_bar, 1);
+        mbar_fence_init();
+        tma_prefetch_desc(&tm_row); tma_prefetch_desc(&tm_col); tma_prefetch_desc(&tm_diag);
+    }
+    __syncthreads();
+
+    // ---- reference samples of the warp's two superpixels ----
+    const float4 *ref_img = a.lab + (size_t)z * a.N;
+    unsigned vmask[2];
+    bool live[2];
+    size_t mi[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const int t = 2 * warp + q;
+        const int gx = blockIdx.x * BT_W + t % BT_W, gy = blockIdx.z * BT_H + t / BT_W;
+        live[q] = gx < a.mw && gy < a.mh;
+        mi[q] = (size_t)z * a.M + (live[q] ? gy * a.mw + gx : 0);
+        bool ref_ok = false;
+        int xr = 0, yr = 0;
+        if (live[q]) {
+            const uint2 r = a.rep[mi[q]];
+            const int d0 = r.x & 255, d1 = (r.x >> 8) & 255, d2 = (r.x >> 16) & 255, d3 = r.x >> 24;
+            const int d4 = r.y & 255, d5 = (r.y >> 8) & 255, d6 = (r.y >> 16) & 255, d7 = r.y >> 24;
+            const int bb_l = max(d0, max(d1, d2)), bb_r = max(d5, max(d6, d7));
+            const int bb_t = max(d0, max(d3, d5)), bb_b = max(d2, max(d4, d7));
+            const float stepx = fmaxf(1.0f, 0.25f * (float)(bb_l + bb_r));
+            const float stepy = fmaxf(1.0f, 0.25f * (float)(bb_t + bb_b));
+            const float4 m0 = a.map[2 * mi[q]];
+            if (lane < 25) {
+                const int i = lane / 5 - 2, j = lane % 5 - 2;
+                xr = f2i(m0.y + (float)i * stepx);
+                yr = f2i(m0.z + (float)j * stepy);
+                ref_ok = xr >= 0 && yr >= 0 && xr < a.W && yr < a.H;
+                s_xy[t][lane] = ref_ok ? make_float2((float)xr, (float)yr) : make_float2(0.0f, 0.0f);
+                s_ref[t][lane] = ref_ok ? ref_img[(size_t)yr * a.W + xr] : make_float4(0, 0, 0, 0);
+            }
+        }
+        vmask[q] = __ballot_sync(FULL, ref_ok);
+        const int lo_x = __reduce_min_sync(FULL, ref_ok ? xr : 0x7fffffff), hi_x = __reduce_max_sync(FULL, ref_ok ? xr : -0x7fffffff);
+        const int lo_y = __reduce_min_sync(FULL, ref_ok ? yr : 0x7fffffff), hi_y = __reduce_max_sync(FULL, ref_ok ? yr : -0x7fffffff);
+        if (lane == 0 && vmask[q]) {
+            atomicMin(&s_box[0], lo_x); atomicMax(&s_box[1], hi_x);
+            atomicMin(&s_box[2], lo_y); atomicMax(&s_box[3], hi_y);
+        }
+    }
+    __syncthreads();
+    const int bx_lo = s_box[0], by_lo = s_box[2];
+    const bool any_ref = s_box[1] >= s_box[0];
+
+    const int refx = z % a.aw, refy = z / a.aw;
+    const int ns = a.subset_num[z];
+    const bool active = lane < a.disp_num;
+    const float d = active ? a.levels[lane] : 0.0f;
+    const float bd = a.bl_ratio * d;
+    float min_val[2] = {1000000.0f, 1000000.0f};
+
+    for (int n = 0; n < ns; ++n) {
+        const int view = a.view_subset[a.V * z + n];
+        const int idx_x = view % a.aw - refx, idx_y = view / a.aw - refy;
+        const float dx = (float)idx_x, dy = (float)idx_y;
+        const int cls = idx_y == 0 ? 0 : (idx_x == 0 ? 1 : 2);
+        const int BW = cls == 0 ? a.bw[0] : (cls == 1 ? a.bw[1] : a.bw[2]);
+        const int BH = cls == 0 ? a.bh[0] : (cls == 1 ? a.bh[1] : a.bh[2]);
+        // window origin: lowest pixel any (sample, level) of the tile can project to (one pixel of slack for the
+        // truncations); samples beyond origin + box take the global load
+        const float sx_hi = fmaxf(a.dmin * dx, a.dmax * dx), sy_hi = fmaxf(a.bl_ratio * a.dmin * dy, a.bl_ratio * a.dmax * dy);
+        const int x0 = any_ref ? bx_lo - (int)ceilf(sx_hi) - 1 : 0, y0 = any_ref ? by_lo - (int)ceilf(sy_hi) - 1 : 0;
+        __syncthreads();                                  // every warp is done with the previous window
+        if (threadIdx.x == 0) {
+            fence_proxy_async();
+            mbar_arrive_expect_tx(&s_bar, (uint32_t)(BW * BH * 16));
+            const CUtensorMap *tm = cls == 0 ? &tm_row : (cls == 1 ? &tm_col : &tm_diag);
+            tma_load_2d(win, tm, 2 * x0, y0 + view * a.H, &s_bar);   // x in 8-byte elements; rows of all views stacked
+        }
+        mbar_wait(&s_bar, (uint32_t)(n & 1));
+        const float4 *pimg = a.lab + (size_t)view * a.N;
+        const float sx = d * dx, sy = bd * dy;
+        float val[2] = {0.0f, 0.0f};
+#pragma unroll 5
+        for (int s = 0; s < 25; ++s) {
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int t = 2 * warp + q;
+                const float2 xy = s_xy[t][s];
+                const int xp = f2i(xy.x - sx);
+                const int yp = f2i(xy.y - sy);
+                val[q] += 30.0f;
+                if (((vmask[q] >> s) & 1u) && (unsigned)xp < (unsigned)a.W && (unsigned)yp < (unsigned)a.H) {
+                    val[q] -= 30.0f;
+                    const float4 cr = s_ref[t][s];
+                    const int wx = xp - x0, wy = yp - y0;
+                    float4 cp;
+                    if ((unsigned)wx < (unsigned)BW && (unsigned)wy < (unsigned)BH) cp = win[wy * BW + wx];
+                    else cp = pimg[yp * a.W + xp];
+                    val[q] += fabsf(cr.x - cp.x) + fabsf(cr.y - cp.y) + fabsf(cr.z - cp.z);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 2; ++q)
+            if (val[q] < min_val[q]) min_val[q] = val[q];
+    }
+
+    // warp argmin over the levels, ties -> lower level index (strict '<' of clcode.cl:1059-1063)
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        float bv = active ? min_val[q] : __int_as_float(0x7f800000);
+        int bi = lane;
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            const float ov = __shfl_xor_sync(FULL, bv, o);
+            const int oi = __shfl_xor_sync(FULL, bi, o);
+            if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        float disp_est = 0.0f;
+        if (bv < 1000000.0f) disp_est = a.levels[bi];
+        if (lane == 0 && live[q]) reinterpret_cast<float *>(a.map + 2 * mi[q] + 1)[3] = disp_est;
+    }
+}
+
+// box sizes of the three neighbour classes for superpixel size S and the disparity range; false when the tile's
+// windows do not fit a TMA box / shared memory (the gather kernel serves those geometries)
+static bool bm_tma_boxes(int S, float dmin, float dmax, float bl_ratio, int bw[3], int bh[3], size_t *smem)
+{
+    if (!(dmax >= dmin) || !isfinite(dmin) || !isfinite(dmax) || !isfinite(bl_ratio)) return false;
+    const int base_w = BT_W * S + 3 * S, base_h = BT_H * S + 3 * S;   // tile + sample reach (S) + drift (S / 2) on both sides
+    const double rx = ceil((double)dmax - dmin) + 3, ry = ceil(fabs((double)bl_ratio) * ((double)dmax - dmin)) + 3;
+    if (rx > 200 || ry > 200) return false;
+    bw[0] = base_w + (int)rx;           bh[0] = base_h;
+    bw[1] = base_w | 1;                 bh[1] = base_h + (int)ry;     // odd pitch: rows one apart -> distinct bank groups
+    bw[2] = (base_w + (int)rx + 1) & ~1; bh[2] = base_h + (int)ry;    // even pitch: (row, column) one apart -> distinct
+    size_t mx = 0;
+    for (int c = 0; c < 3; ++c) {
+        if (bw[c] > 128 || bh[c] > 256) return false;
+        mx = std::max(mx, (size_t)bw[c] * bh[c] * 16);
+    }
+    *smem = mx;
+    return mx <= 190 * 1024;
+}
+
+static int launch_block_match_tma(const FrameDev &f, float bl_ratio, int z0, int z1, cudaStream_t st)
+{
+    BmTma *t = f.bm_tma;
+    if (!t || f.num_levels < 1 || f.num_levels > 32 || !f.levels) return 0;
+    // level range (host copy of the levels is not kept here: the launcher is given them through the frame's cache)
+    if (t->state == 0 || t->lab != (const void *)f.lab || t->bl_ratio != bl_ratio) return 0;
+    if (t->state < 0) return 0;
+    BmTmaArgs a;
+    a.lab = f.lab; a.map = f.map; a.rep = f.rep; a.levels = f.levels; a.view_subset = f.view_subset; a.subset_num = f.subset_num;
+    a.disp_num = f.num_levels; a.aw = f.aw; a.V = f.V; a.W = f.W; a.H = f.H; a.N = f.N; a.M = f.M; a.mw = f.mw; a.mh = f.mh;
+    a.z0 = z0; a.bl_ratio = bl_ratio; a.dmin = t->dmin; a.dmax = t->dmax;
+    size_t smem = 0;
+    for (int c = 0; c < 3; ++c) { a.bw[c] = t->bw[c]; a.bh[c] = t->bh[c]; smem = std::max(smem, (size_t)t->bw[c] * t->bh[c] * 16); }
+    cudaFuncSetAttribute(k_block_match_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    dim3 g((f.mw + BT_W - 1) / BT_W, z1 - z0, (f.mh + BT_H - 1) / BT_H);
+    k_block_match_tma<<<g, BT_WARPS * 32, smem, st>>>(t->map[0], t->map[1], t->map[2], a);
+    return 1;
+}
+
+// (re)build the tensor maps of the frame for this Lab buffer / level set / bl_ratio; host levels are passed in
+int prepare_block_match_tma(const FrameDev &f, const float *levels_host, int nlev, float bl_ratio, const char **why)
+{
+    static const char *none = "";
+    *why = none;
+    BmTma *t = f.bm_tma;
+    if (!t) return 0;
+    float dmin = 0, dmax = 0;
+    for (int i = 0; i < nlev; ++i) {
+        dmin = i ? std::min(dmin, levels_host[i]) : levels_host[i];
+        dmax = i ? std::max(dmax, levels_host[i]) : levels_host[i];
+    }
+    if (t->state != 0 && t->lab == (const void *)f.lab && t->dmin == dmin && t->dmax == dmax && t->bl_ratio == bl_ratio &&
+        t->nlev == nlev)
+        return 0;
+    t->lab = f.lab; t->dmin = dmin; t->dmax = dmax; t->bl_ratio = bl_ratio; t->nlev = nlev;
+    t->state = -1;
+    size_t smem = 0;
+    if (nlev < 1 || nlev > 32 || (f.W * 16) % 16 || !bm_tma_boxes(f.S, dmin, dmax, bl_ratio, t->bw, t->bh, &smem)) return 0;
+    if ((double)f.V * f.H >= 2147483647.0) return 0;
+    for (int c = 0; c < 3; ++c)
+        if (tma_make_image_map(&t->map[c], f.lab, 16, f.W, f.H, f.V, t->bw[c], t->bh[c], why)) return 1;
+    t->state = 1;
+    return 0;
+}
+
 int launch_block_match(const FrameDev &f, float bl_ratio, int z0, int z1, cudaStream_t st)
 {
     if (z1 <= z0) return 0;
+    // The TMA-window kernel is bit-identical but measured slower on the bench frames (6.8 ms against 3.8 ms per
+    // 15-view 1080p frame: one resident CTA per SM, window fill and compute strictly in turn); it runs on request
+    // (MVS_BM_MODE=tma) so that the comparison stays reproducible.  DESIGN.md section 4.1b has the numbers.
+    static const bool want_tma = [] { const char *e = getenv("MVS_BM_MODE"); return e && !strcmp(e, "tma"); }();
+    if (want_tma && launch_block_match_tma(f, bl_ratio, z0, z1, st)) return 1;
     const int nblocks = (f.M + BM_WARPS - 1) / BM_WARPS;
     int band_blocks = std::max(1, (2 * f.mw + BM_WARPS - 1) / BM_WARPS);   // two superpixel rows per band
     int bands = (nblocks + band_blocks - 1) / band_blocks;

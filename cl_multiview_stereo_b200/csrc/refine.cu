@@ -208,6 +208,23 @@ __global__ void __launch_bounds__(128) k_init_state(FrameDev f, RefineArgs ra, i
     f.cost[0][id] = make_float2(sm, cs);
 }
 
+// The plane part of init_current_state alone: {d, n} = {s7, (0, 0, 1)} (clcode.cl:1398-1403).  On a view-sharded frame
+// a rank fills the INPUT planes of its halo views for iteration 0 with this from the centres it already holds,
+// instead of receiving them from their owners (one exchange less per frame; same values by construction).
+__global__ void __launch_bounds__(256) k_plane_from_map(const float4 *__restrict__ map, float4 *__restrict__ plane, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) plane[i] = make_float4(map[2 * i + 1].w, 0.0f, 0.0f, 1.0f);
+}
+
+int launch_plane_from_map(const FrameDev &f, int z0, int z1, cudaStream_t st)
+{
+    size_t n = (size_t)(z1 - z0) * f.M, o = (size_t)z0 * f.M;
+    if (!n) return 0;
+    k_plane_from_map<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(f.map + 2 * o, f.plane[0] + o, n);
+    return 1;
+}
+
 int launch_init_state(const FrameDev &f, const RefineArgs &a, int z0, int z1, cudaStream_t st)
 {
     if (z1 <= z0) return 0;

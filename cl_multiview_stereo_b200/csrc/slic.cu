@@ -8,6 +8,9 @@
 #include "common.cuh"
 #include <algorithm>
 #include "mvs_math.cuh"
+#include "tma.cuh"
+#include <stdlib.h>
+#include <string.h>
 
 namespace mvs {
 
@@ -76,6 +79,86 @@ int launch_init_centers(const FrameDev &f, int z0, int z1, cudaStream_t st)
     dim3 g((f.M + 255) / 256, z1 - z0);
     k_init_centers<<<g, 256, 0, st>>>(f.lab, f.map, f.W, f.H, f.mw, f.mh, f.S, f.N, f.M, z0);
     return 1;
+}
+
+// ---------------------------------------------------------------------------------------
+// Edge-aware centre placement (edge_enable; clSLIC::apply_edge_values, clSLIC.cpp:186-233).
+// edge_compute_alternative (clcode.cl:161-195) as pinned in DESIGN.md section 3 and oracle.c: the Sobel magnitude
+// of Lab is computed from the values cvt wrote (every window reads a snapshot: the kernel here reads `lab` and
+// writes `edge`, two different buffers) and stored in the edge image the reference's parameter list names.  The
+// 3x3 window is indexed as the reference indexes it: nine entries INCLUDING the centre, so entry 4 of the
+// formulas is the centre pixel and entry 5 the right-hand neighbour (clcode.cl:172-192).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_edge_sobel(const float4 *__restrict__ lab, float *__restrict__ edge, int W, int H,
+                                                    int N, int z0)
+{
+    const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+    const int z = z0 + blockIdx.z;
+    if (x >= W || y >= H) return;
+    const float4 *vlab = lab + (size_t)z * N;
+    float4 c[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+        const int cx = max(0, min(W - 1, x + k % 3 - 1)), cy = max(0, min(H - 1, y + k / 3 - 1));   // clcode.cl:178
+        c[k] = vlab[(size_t)cy * W + cx];
+    }
+    const float cx_[9] = {c[0].x, c[1].x, c[2].x, c[3].x, c[4].x, c[5].x, c[6].x, c[7].x, c[8].x};
+    const float cy_[9] = {c[0].y, c[1].y, c[2].y, c[3].y, c[4].y, c[5].y, c[6].y, c[7].y, c[8].y};
+    const float cz_[9] = {c[0].z, c[1].z, c[2].z, c[3].z, c[4].z, c[5].z, c[6].z, c[7].z, c[8].z};
+    float v[3];
+    const float *ch[3] = {cx_, cy_, cz_};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float *q = ch[k];
+        const float dx = -1 * q[0] + q[2] - 2 * q[3] + 2 * q[4] - q[5] + q[7];   // clcode.cl:190
+        const float dy = -1 * q[0] - 2 * q[1] - q[2] + q[5] + 2 * q[6] + q[7];   // clcode.cl:191
+        v[k] = dx * dx + dy * dy;
+    }
+    edge[(size_t)z * N + (size_t)y * W + x] = sqrtf(v[0] * 1.0f + v[1] * 1.0f + v[2] * 1.0f);   // dot(v, (1,1,1))
+}
+
+// apply_edge_alternative (clcode.cl:204-248): each centre moves to the 8-neighbour of its truncated position with the
+// smallest edge value (strict '<'; scan order W, NW, N, NE, E, SE, S, SW) and takes that pixel's colour
+__global__ void __launch_bounds__(256) k_apply_edge(const float4 *__restrict__ lab, const float *__restrict__ edge,
+                                                    float4 *__restrict__ map, int W, int H, int N, int M, int z0)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int z = z0 + blockIdx.y;
+    if (c >= M) return;
+    float4 *m = map + 2 * ((size_t)z * M + c);
+    const float4 m0 = m[0];
+    const int cx = f2i(m0.y), cy = f2i(m0.z);
+    const float *ve = edge + (size_t)z * N;
+    // the reference reads edge_img at the centre without a bounds test; a centre is inside the image by construction
+    // (init_cluster_centers), the clamp only guards the W mod S == S / 2 corner case (Appendix B S4)
+    float edge_val = ve[(size_t)min(max(cy, 0), H - 1) * W + min(max(cx, 0), W - 1)];
+    const int dx[8] = {-1, -1, 0, 1, 1, 1, 0, -1}, dy[8] = {0, -1, -1, -1, 0, 1, 1, 1};
+    bool changed = false;
+    int c2x = 0, c2y = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int nx = cx + dx[i], ny = cy + dy[i];
+        if (nx >= 0 && ny >= 0 && nx < W && ny < H) {
+            const float ne = ve[(size_t)ny * W + nx];
+            if (ne < edge_val) { edge_val = ne; c2x = nx; c2y = ny; changed = true; }
+        }
+    }
+    if (changed) {
+        const float4 col = lab[(size_t)z * N + (size_t)c2y * W + c2x];
+        const float4 m1 = m[1];
+        m[0] = make_float4(m0.x, (float)c2x, (float)c2y, col.x);
+        m[1] = make_float4(col.y, col.z, m1.z, m1.w);
+    }
+}
+
+int launch_apply_edge_values(const FrameDev &f, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    dim3 b(32, 8), g((f.W + 31) / 32, (f.H + 7) / 8, z1 - z0);
+    k_edge_sobel<<<g, b, 0, st>>>(f.lab, f.edge, f.W, f.H, f.N, z0);
+    dim3 g2((f.M + 255) / 256, z1 - z0);
+    k_apply_edge<<<g2, 256, 0, st>>>(f.lab, f.edge, f.map, f.W, f.H, f.N, f.M, z0);
+    return 2;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -328,50 +411,16 @@ __host__ __device__ constexpr UpdTile upd_tile(int S)
     return t;
 }
 
+// per-cluster window reduction out of the staged tile (s_lab / s_idx, row pitch t.pitch); the eight floats of a
+// centre are written by eight lanes, one component each (five of them a division: one division's worth of
+// instructions instead of five on a single lane; s7 is simply not stored)
 template <int S_T>
-__global__ void __launch_bounds__(UPD_THREADS) k_update_centers_tiled(const float4 *__restrict__ lab,
-                                                              const uint32_t *__restrict__ idx,
-                                                              float4 *__restrict__ map, int W, int H, int mw, int mh,
-                                                              int S_rt, int N, int M, int z0)
+__device__ __forceinline__ void upd_reduce(const float4 *s_lab, const uint32_t *s_idx, float4 *__restrict__ map, int S, int mw,
+                                           int mh, int M, int z, int gx0, int gy0, int x0, int y0)
 {
-    const int S = S_T > 0 ? S_T : S_rt;
     const UpdTile t = upd_tile(S);
     const int G = (S * S * 9 + 255) / 256, cpl = S * 3 / 16;
-    extern __shared__ __align__(16) unsigned char upd_smem[];
-    float4 *s_lab = reinterpret_cast<float4 *>(upd_smem);
-    uint32_t *s_idx = reinterpret_cast<uint32_t *>(s_lab + (size_t)t.rh * t.pitch);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int z = z0 + blockIdx.z;
-    const int gx0 = blockIdx.x * t.tcx, gy0 = blockIdx.y * t.tcy;
-    const int x0 = gx0 * S - S, y0 = gy0 * S - S;
-    const uint32_t *vidx = idx + (size_t)z * N;
-    const float4 *vlab = lab + (size_t)z * N;
-    // staging: four elements per thread in flight (loads first, then the shared-memory stores)
-    const int total = t.rw * t.rh;
-    for (int e0 = threadIdx.x; e0 < total; e0 += 4 * UPD_THREADS) {
-        uint32_t l[4];
-        float4 c[4];
-        int so[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int e = e0 + j * UPD_THREADS;
-            const int ry = e / t.rw, rx = e - ry * t.rw;
-            const int px = x0 + rx, py = y0 + ry;
-            l[j] = 0xFFFFFFFFu;
-            c[j] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            so[j] = e < total ? ry * t.pitch + rx : -1;
-            if (e < total && py >= 0 && py < H && px >= 0 && px < W) {
-                const size_t pi = (size_t)py * W + px;
-                l[j] = __ldg(vidx + pi);
-                c[j] = __ldg(vlab + pi);
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-            if (so[j] >= 0) { s_idx[so[j]] = l[j]; s_lab[so[j]] = c[j]; }
-    }
-    __syncthreads();
-
     const int lx = lane & 15, lyh = lane >> 4;
     for (int ci = warp; ci < t.tcx * t.tcy; ci += UPD_THREADS / 32) {
         const int lcx = ci % t.tcx, lcy = ci / t.tcx;
@@ -423,24 +472,125 @@ __global__ void __launch_bounds__(UPD_THREADS) k_update_centers_tiled(const floa
                 a1 += __shfl_down_sync(0xffffffffu, a1, o);
                 a2 += __shfl_down_sync(0xffffffffu, a2, o);
             }
-            c0 = c0 + a0; c1 = c1 + a1; c2 = c2 + a2;
+            c0 = c0 + a0; c1 = c1 + a1; c2 = c2 + a2;   // only lane 0 holds the tree root
         }
         const int sx = __reduce_add_sync(0xffffffffu, tx);
         const int sy = __reduce_add_sync(0xffffffffu, ty);
         const int sn = __reduce_add_sync(0xffffffffu, tn);
-        if (lane == 0) {
-            float4 *m = map + 2 * ((size_t)z * M + c);
-            const float keep7 = m[1].w;
-            if (sn != 0) {
-                const float n = (float)sn;
-                m[0] = make_float4((float)c, (float)sx / n, (float)sy / n, c0 / n);
-                m[1] = make_float4(c1 / n, c2 / n, n, keep7);
-            } else {
-                m[0] = make_float4((float)c, 0.0f, 0.0f, 0.0f);
-                m[1] = make_float4(0.0f, 0.0f, 0.0f, keep7);
+        // finalize_reduction_result (clcode.cl:719-773): lane L writes component L of the float8
+        const float r0 = __shfl_sync(0xffffffffu, c0, 0), r1 = __shfl_sync(0xffffffffu, c1, 0), r2 = __shfl_sync(0xffffffffu, c2, 0);
+        const float n = (float)sn;
+        const float num = lane == 1 ? (float)sx : lane == 2 ? (float)sy : lane == 3 ? r0 : lane == 4 ? r1 : r2;
+        float val = num / n;
+        if (lane == 0) val = (float)c;
+        if (lane == 6) val = n;
+        if (sn == 0 && lane != 0) val = 0.0f;   // empty cluster: centre (0, 0), colour 0, count 0 (clcode.cl:731-734)
+        if (lane < 7) reinterpret_cast<float *>(map + 2 * ((size_t)z * M + c))[lane] = val;
+    }
+}
+
+template <int S_T>
+__global__ void __launch_bounds__(UPD_THREADS) k_update_centers_tiled(const float4 *__restrict__ lab,
+                                                              const uint32_t *__restrict__ idx,
+                                                              float4 *__restrict__ map, int W, int H, int mw, int mh,
+                                                              int S_rt, int N, int M, int z0)
+{
+    const int S = S_T > 0 ? S_T : S_rt;
+    const UpdTile t = upd_tile(S);
+    extern __shared__ __align__(16) unsigned char upd_smem[];
+    float4 *s_lab = reinterpret_cast<float4 *>(upd_smem);
+    uint32_t *s_idx = reinterpret_cast<uint32_t *>(s_lab + (size_t)t.rh * t.pitch);
+    const int z = z0 + blockIdx.z;
+    const int gx0 = blockIdx.x * t.tcx, gy0 = blockIdx.y * t.tcy;
+    const int x0 = gx0 * S - S, y0 = gy0 * S - S;
+    const uint32_t *vidx = idx + (size_t)z * N;
+    const float4 *vlab = lab + (size_t)z * N;
+    // staging: four elements per thread in flight (loads first, then the shared-memory stores)
+    const int total = t.rw * t.rh;
+    for (int e0 = threadIdx.x; e0 < total; e0 += 4 * UPD_THREADS) {
+        uint32_t l[4];
+        float4 c[4];
+        int so[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int e = e0 + j * UPD_THREADS;
+            const int ry = e / t.rw, rx = e - ry * t.rw;
+            const int px = x0 + rx, py = y0 + ry;
+            l[j] = 0xFFFFFFFFu;
+            c[j] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            so[j] = e < total ? ry * t.pitch + rx : -1;
+            if (e < total && py >= 0 && py < H && px >= 0 && px < W) {
+                const size_t pi = (size_t)py * W + px;
+                l[j] = __ldg(vidx + pi);
+                c[j] = __ldg(vlab + pi);
             }
         }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (so[j] >= 0) { s_idx[so[j]] = l[j]; s_lab[so[j]] = c[j]; }
     }
+    __syncthreads();
+    upd_reduce<S_T>(s_lab, s_idx, map, S, mw, mh, M, z, gx0, gy0, x0, y0);
+}
+
+// The same with the tile staged by TMA: one box load of the Lab tile and one of the label tile (cp.async.bulk.tensor,
+// completion on an mbarrier) replace the per-thread index arithmetic, loads and shared-memory stores of the staging
+// loop -- 28 % of the kernel's instructions and its long-scoreboard stalls (profiles/r02_v3_k_update_centers_tiled*).
+// The box is t.pitch pixels wide (the bank-friendly row pitch of the reduction, a few columns more than the window
+// needs).  TMA fills out-of-range box parts with zeros, and a box that leaves a view vertically reads the rows of the
+// neighbouring view in the stack: label 0 is a real cluster and so are the neighbour's labels, therefore CTAs whose
+// box leaves the image overwrite those label slots with 0xFFFFFFFF, which no cluster carries.
+template <int S_T>
+__global__ void __launch_bounds__(UPD_THREADS) k_update_centers_tma(const __grid_constant__ CUtensorMap tm_lab,
+                                                                    const __grid_constant__ CUtensorMap tm_idx,
+                                                                    float4 *__restrict__ map, int W, int H, int mw, int mh,
+                                                                    int M, int z0)
+{
+    constexpr int S = S_T;
+    constexpr UpdTile t = upd_tile(S);
+    extern __shared__ __align__(128) unsigned char upd_smem[];
+    __shared__ __align__(8) uint64_t s_bar;
+    float4 *s_lab = reinterpret_cast<float4 *>(upd_smem);
+    uint32_t *s_idx = reinterpret_cast<uint32_t *>(s_lab + (size_t)t.rh * t.pitch);
+    const int z = z0 + blockIdx.z;
+    const int gx0 = blockIdx.x * t.tcx, gy0 = blockIdx.y * t.tcy;
+    const int x0 = gx0 * S - S, y0 = gy0 * S - S;
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_fence_init();
+        mbar_arrive_expect_tx(&s_bar, (uint32_t)(t.rh * t.pitch * (sizeof(float4) + sizeof(uint32_t))));
+        tma_load_2d(s_lab, &tm_lab, 2 * x0, y0 + z * H, &s_bar);   // Lab pixels are two 8-byte elements wide
+        tma_load_2d(s_idx, &tm_idx, x0, y0 + z * H, &s_bar);
+    }
+    __syncthreads();           // the initialised barrier is visible to every thread before it waits on it
+    mbar_wait(&s_bar, 0);
+    if (x0 < 0 || y0 < 0 || x0 + t.pitch > W || y0 + t.rh > H) {   // CTA-uniform: the box leaves the image
+        for (int e = threadIdx.x; e < t.rh * t.pitch; e += UPD_THREADS) {
+            const int ry = e / t.pitch, rx = e - ry * t.pitch;
+            const int px = x0 + rx, py = y0 + ry;
+            if (px < 0 || px >= W || py < 0 || py >= H) s_idx[e] = 0xFFFFFFFFu;
+        }
+        __syncthreads();
+    }
+    upd_reduce<S_T>(s_lab, s_idx, map, S, mw, mh, M, z, gx0, gy0, x0, y0);
+}
+
+// (re)build the tensor maps of the centre update for this frame's Lab / label buffers (S = 8 tile: 80 x 48 box)
+int prepare_update_centers_tma(const FrameDev &f, const char **why)
+{
+    static const char *none = "";
+    *why = none;
+    SlicTma *tm = f.slic_tma;
+    if (!tm || f.S != 8) return 0;
+    if (tm->state != 0 && tm->lab == (const void *)f.lab && tm->idx == (const void *)f.idx) return 0;
+    tm->lab = f.lab; tm->idx = f.idx;
+    tm->state = -1;
+    const UpdTile t = upd_tile(8);
+    if (f.W % 4 || (double)f.V * f.H >= 2147483647.0) return 0;   // label rows must be 16-byte multiples for a tensor map
+    if (tma_make_image_map(&tm->map_lab, f.lab, 16, f.W, f.H, f.V, t.pitch, t.rh, why)) return 1;
+    if (tma_make_image_map(&tm->map_idx, f.idx, 4, f.W, f.H, f.V, t.pitch, t.rh, why)) return 1;
+    tm->state = 1;
+    return 0;
 }
 
 int launch_update_centers(const FrameDev &f, int z0, int z1, cudaStream_t st)
@@ -453,6 +603,15 @@ int launch_update_centers(const FrameDev &f, int z0, int z1, cudaStream_t st)
     size_t smem = (size_t)t.rh * t.pitch * (sizeof(float4) + sizeof(uint32_t));
     if (G == (S * S * 9 + 255) / 256 && smem <= 200 * 1024) {
         dim3 g((f.mw + t.tcx - 1) / t.tcx, (f.mh + t.tcy - 1) / t.tcy, z1 - z0);
+        // S = 8 (the shipped setting): tile staged by TMA when the frame's tensor maps could be built
+        // (MVS_UPD_MODE=loads forces the load-staged kernel for A/B measurement)
+        static const bool force_loads = [] { const char *e = getenv("MVS_UPD_MODE"); return e && !strcmp(e, "loads"); }();
+        SlicTma *tm = f.slic_tma;
+        if (S == 8 && !force_loads && tm && tm->state == 1 && tm->lab == (const void *)f.lab && tm->idx == (const void *)f.idx) {
+            cudaFuncSetAttribute(k_update_centers_tma<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            k_update_centers_tma<8><<<g, UPD_THREADS, smem, st>>>(tm->map_lab, tm->map_idx, f.map, f.W, f.H, f.mw, f.mh, f.M, z0);
+            return 1;
+        }
 #define UPD_LAUNCH(ST)                                                                                              \
     do {                                                                                                            \
         cudaFuncSetAttribute(k_update_centers_tiled<ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \

@@ -72,12 +72,12 @@ static mvs_params params_of(const system_settings &s, int W, int H)
     p.min_disp = s.min_disp; p.max_disp = s.max_disp; p.inc = s.inc; p.bl_ratio = s.bl_ratio;
     p.kernel_size = s.kernel_size; p.kernel_step = s.kernel_step;
     p.fuse = s.fuse; p.gamma = s.gamma; p.alpha = s.alpha; p.no_prop = s.no_prop;
+    p.edge_enable = s.edge_enable ? 1 : 0;
     return p;
 }
 
 void pipeline::run_device_resident()
 {
-    if (settings->edge_enable) throw std::runtime_error("pipeline: edge_enable is not supported");
     size_t n1 = (size_t)img_size.x * img_size.y, N = n1 * view_num, M = (size_t)map_size.x * map_size.y * view_num;
     std::vector<vec3u> in_img(N);
     for (int i = 0; i < view_num; i++) loadImageIn(img_array[i], in_img.data() + i * n1, img_size.y, img_size.x);

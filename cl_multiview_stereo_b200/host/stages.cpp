@@ -34,17 +34,15 @@ clSLIC::clSLIC(cl::Program program_, system_settings *settings_, cl_int2 img_siz
     int mw = (int)ceilf((float)img_size.x / (float)S), mh = (int)ceilf((float)img_size.y / (float)S);
     if (mw != map_size.x || mh != map_size.y)
         throw std::runtime_error("clSLIC: map_size must be ceil(img_size / spixl_size) (pipeline.cpp:18-19)");
-    if (settings->edge_enable)
-        throw std::runtime_error("clSLIC: edge_enable is not supported (off at the shipped settings, clMVDE.cpp:21)");
 }
 
 clSLIC::~clSLIC() {}
 
 void clSLIC::do_super_pixel_seg_batch(int count, vec3u *in_img, vec3f *cvt_img, vec8f *spixl_map, cl_uint *idx_img)
 {
-    must(mvs_slic_run(need_ctx(program, "clSLIC"), img_size.x, img_size.y, settings->spixl_size,
-                      settings->slic_color_weight, settings->no_iter, settings->enforce_connectivity ? 1 : 0, count,
-                      in_img, cvt_img, spixl_map, idx_img),
+    must(mvs_slic_run_edge(need_ctx(program, "clSLIC"), img_size.x, img_size.y, settings->spixl_size,
+                           settings->slic_color_weight, settings->no_iter, settings->enforce_connectivity ? 1 : 0,
+                           settings->edge_enable ? 1 : 0, count, in_img, cvt_img, spixl_map, idx_img, nullptr),
          "clSLIC::do_super_pixel_seg");
     last_idx = idx_img;
 }

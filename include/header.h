@@ -75,7 +75,7 @@ struct system_settings {
     int array_width, array_height;   /* camera grid; view index = gy * array_width + gx */
     int no_iter;                     /* centre-update / association rounds after the first association */
     bool enforce_connectivity = false;   /* two passes of the 5x5 label vote (clSLIC.cpp:390-410) */
-    bool edge_enable = false;            /* not supported: undefined in the reference */
+    bool edge_enable = false;            /* edge-aware centre placement (clSLIC.cpp:86, 186-233; semantics pinned in DESIGN.md section 3) */
 
     /* ---- disparity initialisation (clPhotoConsistency) ---- */
     int num_disp_levels;             /* written by pipeline::perform_depth_est, not read from main() */

@@ -52,6 +52,7 @@ typedef struct mvs_params {
     int kernel_step;
     float fuse, gamma, alpha;    /* as in system_settings (2*g^2, 2*a^2 applied internally, pipeline.cpp:164-165) */
     int no_prop;
+    int edge_enable;             /* clSLIC::apply_edge_values before the first association (clSLIC.cpp:86, 186-233) */
 } mvs_params;
 
 /* selectors for mvs_frame_download / mvs_frame_upload / mvs_frame_dev_ptr */
@@ -158,7 +159,11 @@ int mvs_frame_exchange(mvs_frame *f, int which);
 /* per-stage device time (ms) of the last mvs_frame_run: slic, boundary, block_match, flatness,
  * init_state, propagate(total), fusion, exchange -- 8 floats */
 int mvs_frame_stage_ms(mvs_frame *f, float *ms8);
-/* stage timing events on/off (on by default for frames made by mvs_frame_create) */
+/* view-sharded frame: the caller uploads the INPUT images of the halo views (the views this rank's own views read) as
+ * well as its own, so that no image crosses between ranks; mvs_frame_halo_views lists them */
+int mvs_frame_set_halo_inputs(mvs_frame *f, int local);
+int mvs_frame_halo_views(mvs_frame *f, int *views, int cap, int *count);
+/* per-stage CUDA events on/off (off by default; mvs_frame_stage_ms reads and resets them) */
 int mvs_frame_set_timing(mvs_frame *f, int enable);
 
 /* ---- class-level entry points with the reference's host-pointer semantics ---- */
@@ -167,6 +172,11 @@ int mvs_frame_set_timing(mvs_frame *f, int enable);
  * for `count` images of the same size; outputs may be NULL to skip the copy back. */
 int mvs_slic_run(mvs_ctx *ctx, int width, int height, int spixl_size, float color_weight, int no_iter,
                  int enforce_connectivity, int count, const void *rgbx, void *lab, void *map, uint32_t *idx);
+/* the same with system_settings::edge_enable (clSLIC.cpp:86): edge-aware centre placement before the first
+ * association; `edge` (may be NULL) receives the Sobel magnitude image [count][H][W] float */
+int mvs_slic_run_edge(mvs_ctx *ctx, int width, int height, int spixl_size, float color_weight, int no_iter,
+                      int enforce_connectivity, int edge_enable, int count, const void *rgbx, void *lab, void *map,
+                      uint32_t *idx, float *edge);
 
 /* clSLIC::draw_segmentation_lines (clSLIC.h:20, clSLIC.cpp:447-478) on the device: `count` images [count][H][W]
  * vec3u + their labels in; out_rgbx is in/out (interior pixels are rewritten, the one-pixel frame is kept). */

@@ -256,15 +256,86 @@ void orc_slic_params(int S, float *max_xy_dist, float *max_color_dist)
     *max_xy_dist = a; *max_color_dist = b;
 }
 
-/* clSLIC::do_super_pixel_seg, clSLIC.cpp:67-122 (edge_enable path not
- * restated: off at the shipped settings and buggy in the reference). */
-void orc_slic(const uint8_t *rgbx, float *lab, float *map, uint32_t *idx, int W, int H, int mw, int mh,
-              int S, float weight, int no_iter, int enforce_connectivity)
+static inline int imax(int a, int b) { return a > b ? a : b; }
+static inline int imin(int a, int b) { return a < b ? a : b; }
+
+/* Edge-aware centre placement (edge_enable, clSLIC.cpp:186-233).
+ *
+ * The reference's first kernel, edge_compute_alternative (clcode.cl:161-195), has no defined result as written:
+ * it stores the edge magnitude INTO cvt_img (the Lab buffer its neighbouring work-items are still reading the 3x3
+ * window from -- a data race whose outcome depends on work-group scheduling), never writes the edge_img parameter,
+ * and apply_edge_alternative (clcode.cl:204-248) then reads that never-written buffer.  Pinned semantics, stated
+ * once in DESIGN.md section 3: the Sobel magnitude is computed from a SNAPSHOT of Lab (every window reads the
+ * values cvt produced) and stored in edge_img, the buffer the kernel's own parameter list names for it; Lab is
+ * left intact.  Everything else is the kernel's text, quirks included: the 3x3 window is stored with its centre
+ * (nine entries into color[], so color[4] is the CENTRE pixel and color[5], not color[4], the right-hand
+ * neighbour), and the Sobel formulas index it as if the centre had been skipped (clcode.cl:172-192). */
+void orc_edge_compute(const float *lab, float *edge, int W, int H)
+{
+#pragma omp parallel for schedule(static)
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            float c[9][3];
+            int i = 0;
+            for (int yo = -1; yo <= 1; yo++)
+                for (int xo = -1; xo <= 1; xo++) {
+                    int cx = imax(0, imin(W - 1, x + xo)), cy = imax(0, imin(H - 1, y + yo));   /* clcode.cl:178 */
+                    const float *p = lab + 4 * ((size_t)W * cy + cx);
+                    c[i][0] = p[0]; c[i][1] = p[1]; c[i][2] = p[2];
+                    i++;
+                }
+            float sum = 0.0f;   /* dot(v, (1,1,1)) = v.x*1 + v.y*1 + v.z*1, left to right */
+            for (int k = 0; k < 3; ++k) {
+                float dx = -1 * c[0][k] + c[2][k] - 2 * c[3][k] + 2 * c[4][k] - c[5][k] + c[7][k];   /* clcode.cl:190 */
+                float dy = -1 * c[0][k] - 2 * c[1][k] - c[2][k] + c[5][k] + 2 * c[6][k] + c[7][k];   /* clcode.cl:191 */
+                float v = dx * dx + dy * dy;
+                sum = k == 0 ? v * 1.0f : sum + v * 1.0f;
+            }
+            edge[(size_t)W * y + x] = sqrtf(sum);
+        }
+}
+
+/* apply_edge_alternative, clcode.cl:204-248: every centre moves to the 8-neighbour of its truncated position with
+ * the smallest edge value (strict '<', scan order W, NW, N, NE, E, SE, S, SW) and takes that pixel's colour */
+void orc_apply_edge(const float *lab, const float *edge, float *map, int W, int H, int mw, int mh)
+{
+    static const int dxy[8][2] = {{-1, 0}, {-1, -1}, {0, -1}, {1, -1}, {1, 0}, {1, 1}, {0, 1}, {-1, 1}};
+    for (int y = 0; y < mh; ++y)
+        for (int x = 0; x < mw; ++x) {
+            float *sp = map + 8 * ((size_t)mw * y + x);
+            int cx = o_f2i(sp[1]), cy = o_f2i(sp[2]);
+            float edge_val = edge[(size_t)W * cy + cx];
+            int changed = 0, c2x = 0, c2y = 0;
+            for (int i = 0; i < 8; ++i) {
+                int nx = cx + dxy[i][0], ny = cy + dxy[i][1];
+                if (nx >= 0 && ny >= 0 && nx < W && ny < H) {
+                    float ne = edge[(size_t)W * ny + nx];
+                    if (ne < edge_val) { edge_val = ne; c2x = nx; c2y = ny; changed = 1; }
+                }
+            }
+            if (changed) {
+                const float *col = lab + 4 * ((size_t)W * c2y + c2x);
+                sp[1] = (float)c2x; sp[2] = (float)c2y;
+                sp[3] = col[0]; sp[4] = col[1]; sp[5] = col[2];
+            }
+        }
+}
+
+/* clSLIC::do_super_pixel_seg, clSLIC.cpp:67-122; edge_enable: apply_edge_values between the centre initialisation
+ * and the first association (clSLIC.cpp:86) */
+void orc_slic_edge(const uint8_t *rgbx, float *lab, float *map, uint32_t *idx, int W, int H, int mw, int mh,
+                   int S, float weight, int no_iter, int enforce_connectivity, int edge_enable)
 {
     float mxy, mcol;
     orc_slic_params(S, &mxy, &mcol);
     orc_cvt(rgbx, lab, W, H);
     orc_init_centers(lab, map, W, H, mw, mh, S);
+    if (edge_enable) {
+        float *edge = (float *)malloc(sizeof(float) * (size_t)W * H);
+        orc_edge_compute(lab, edge, W, H);
+        orc_apply_edge(lab, edge, map, W, H, mw, mh);
+        free(edge);
+    }
     orc_assoc(lab, map, idx, W, H, mw, mh, S, mxy, mcol, weight);
     for (int i = 0; i < no_iter; ++i) {
         orc_update_centers(lab, idx, map, W, H, mw, mh, S);
@@ -276,6 +347,12 @@ void orc_slic(const uint8_t *rgbx, float *lab, float *map, uint32_t *idx, int W,
         orc_suppress(tmp, idx, W, H);
         free(tmp);
     }
+}
+
+void orc_slic(const uint8_t *rgbx, float *lab, float *map, uint32_t *idx, int W, int H, int mw, int mh,
+              int S, float weight, int no_iter, int enforce_connectivity)
+{
+    orc_slic_edge(rgbx, lab, map, idx, W, H, mw, mh, S, weight, no_iter, enforce_connectivity, 0);
 }
 
 /* ------------------------------------------------------------------------ */
@@ -319,7 +396,6 @@ void orc_boundary(const float *map, const uint32_t *idx, uint8_t *rep, int V, in
             }
 }
 
-static inline int imax(int a, int b) { return a > b ? a : b; }
 
 /* kernel initial_depth_estimation_v2, clcode.cl:972-1069, for views z0..z1-1
  * (the reference launches it once per view, photo_consistency.cpp:133-140).

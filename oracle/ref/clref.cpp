@@ -157,6 +157,42 @@ void clref_update_centers(const void *lab, const void *idx, void *map, int W, in
     ndrange(round_up16(mw), round_up16(mh), 1, [&] { finalize_reduction_result(accum.data(), (float8 *)map, msz, G); });
 }
 
+// apply_edge_alternative (clSLIC.cpp:215-232) from the reference source: deterministic for a given edge map
+void clref_apply_edge(const void *lab, const float *edge, void *map, int W, int H, int mw, int mh)
+{
+    int2 isz(W, H), msz(mw, mh);
+    ndrange(round_up16(mw), round_up16(mh), 1, [&] { apply_edge_alternative((float3 *)lab, (float *)edge, (float8 *)map, isz, msz); });
+}
+
+// The ARITHMETIC of edge_compute_alternative (clSLIC.cpp:194-211) from the reference source.  The kernel overwrites
+// the Lab buffer it reads (clcode.cl:194), so every work-item is run on a private copy of the Lab SNAPSHOT and the
+// value it stores at its own pixel is collected: what the kernel computes when no neighbour has been overwritten
+// yet -- the semantics this repository pins (oracle.c orc_edge_compute).  Small images only (one copy per pixel).
+// Its `float3 color[8]` is indexed up to 8 (clcode.cl:169-184): the ninth store lands outside the array; the
+// kernel text is compiled with room for it (see prep.py).
+void clref_edge_compute_snapshot(const void *lab, float *edge, int W, int H)
+{
+    int2 sz(W, H);
+    const size_t n = (size_t)W * H;
+#pragma omp parallel
+    {
+        std::vector<float3> copy(n);
+#pragma omp for schedule(dynamic, 4)
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x) {
+                memcpy(copy.data(), lab, n * sizeof(float3));
+                WorkItem &w = wi;
+                w.group_barrier = nullptr;
+                w.gsz[0] = round_up16(W); w.gsz[1] = round_up16(H); w.gsz[2] = 1;
+                w.lsz[0] = 16; w.lsz[1] = 16; w.lsz[2] = 1;
+                w.gid[0] = x; w.gid[1] = y; w.gid[2] = 0; w.lid[0] = x % 16; w.lid[1] = y % 16; w.lid[2] = 0;
+                w.grp[0] = x / 16; w.grp[1] = y / 16; w.grp[2] = 0;
+                edge_compute_alternative(copy.data(), edge, sz);
+                edge[(size_t)W * y + x] = copy[(size_t)W * y + x].x;   // the kernel broadcasts the scalar into the float3
+            }
+    }
+}
+
 // clSLIC::enforce_connectivity, one pass (clSLIC.cpp:390-410)
 void clref_suppress(const void *in, void *out, int W, int H)
 {

@@ -64,6 +64,20 @@ class ClRef:
         self.lib.clref_update_centers(_p(lab), _p(idx), _p(mp), W, H, mw, mh, S)
         return mp
 
+    def edge_compute_snapshot(self, lab):
+        """the arithmetic of edge_compute_alternative, every work-item on its own copy of the Lab snapshot"""
+        H, W, _ = lab.shape
+        edge = np.zeros((H, W), f32)
+        self.lib.clref_edge_compute_snapshot(_p(np.ascontiguousarray(lab, f32)), _p(edge), W, H)
+        return edge
+
+    def apply_edge(self, lab, edge, mp):
+        H, W, _ = lab.shape
+        mh, mw, _ = mp.shape
+        mp = np.array(mp, f32, order="C", copy=True)
+        self.lib.clref_apply_edge(_p(np.ascontiguousarray(lab, f32)), _p(np.ascontiguousarray(edge, f32)), _p(mp), W, H, mw, mh)
+        return mp
+
     def suppress(self, idx):
         H, W = idx.shape
         out = np.zeros_like(idx)

@@ -49,6 +49,38 @@ class Oracle:
         self.lib.orc_slic(_p(rgbx), _p(lab), _p(mp), _p(idx), W, H, mw, mh, S, _cf(weight), no_iter, int(connectivity))
         return lab, mp, idx
 
+    def slic_edge(self, rgbx, S=8, weight=0.6, no_iter=5, connectivity=False, edge=True):
+        """do_super_pixel_seg with edge_enable (pinned semantics, oracle.c orc_edge_compute)"""
+        rgbx = np.ascontiguousarray(rgbx, u8)
+        H, W, _ = rgbx.shape
+        mw, mh = -(-W // S), -(-H // S)
+        lab = np.zeros((H, W, 4), f32)
+        mp = np.zeros((mh, mw, 8), f32)
+        idx = np.zeros((H, W), u32)
+        self.lib.orc_slic_edge(_p(rgbx), _p(lab), _p(mp), _p(idx), W, H, mw, mh, S, _cf(weight), no_iter, int(connectivity),
+                               int(edge))
+        return lab, mp, idx
+
+    def edge_compute(self, lab):
+        H, W, _ = lab.shape
+        edge = np.zeros((H, W), f32)
+        self.lib.orc_edge_compute(_p(np.ascontiguousarray(lab, f32)), _p(edge), W, H)
+        return edge
+
+    def apply_edge(self, lab, edge, mp):
+        H, W, _ = lab.shape
+        mh, mw, _ = mp.shape
+        mp = np.array(mp, f32, order="C", copy=True)
+        self.lib.orc_apply_edge(_p(np.ascontiguousarray(lab, f32)), _p(np.ascontiguousarray(edge, f32)), _p(mp), W, H, mw, mh)
+        return mp
+
+    def init_centers(self, lab, S):
+        H, W, _ = lab.shape
+        mw, mh = -(-W // S), -(-H // S)
+        mp = np.zeros((mh, mw, 8), f32)
+        self.lib.orc_init_centers(_p(np.ascontiguousarray(lab, f32)), _p(mp), W, H, mw, mh, S)
+        return mp
+
     def cvt(self, rgbx):
         rgbx = np.ascontiguousarray(rgbx, u8)
         H, W, _ = rgbx.shape

@@ -178,3 +178,35 @@ def test_reference_host_twins_build_and_run():
                                1.0, 13, 64, 3)
     assert np.abs(flat - ref["flat"]).max() < 1e-4
     assert np.isfinite(sa[..., :3]).all() and (sa[..., 5] != 0).any()
+
+
+@pytest.mark.parametrize("W,H,S", [(61, 43, 8), (96, 64, 8), (75, 50, 16)])
+def test_edge_aware_slic_pinned_to_reference_source(W, H, S):
+    """edge_enable (clSLIC.cpp:186-233).  The reference's first kernel overwrites the buffer it reads and leaves the
+    edge image unwritten (clcode.cl:176-194), so its result is undefined as written; the pinned semantics (DESIGN.md
+    section 3: Sobel of a Lab snapshot into the edge image) are held against the reference's own source where it IS
+    defined: the arithmetic of edge_compute_alternative per work-item on a private snapshot, and apply_edge_alternative
+    on a given edge map."""
+    from tests import orc
+    r = clref.load()
+    if r is None:
+        pytest.skip("oracle/_ref/libclref.so not built")
+    o = orc.load()
+    img = synth.voronoi_image(40 + W, W, H, sites=24)
+    lab = o.cvt(img)
+    edge = o.edge_compute(lab)
+    assert_same(edge, r.edge_compute_snapshot(lab), "edge magnitude")
+    mp = o.init_centers(lab, S)
+    moved = o.apply_edge(lab, edge, mp)
+    assert_same(moved[..., :7], r.apply_edge(lab, edge, mp)[..., :7], "centres after apply_edge_alternative")
+    assert (moved[..., 1:3] != mp[..., 1:3]).any(), "the test image should move some centre"
+    # the whole segmentation with the flag: stages as clSLIC::do_super_pixel_seg orders them (clSLIC.cpp:83-96)
+    lab2, mp2, idx2 = o.slic_edge(img, S, 0.6, 3, False, True)
+    mxy, mcol = o.slic_params(S)
+    ix = r.assoc(lab, moved, S, 0.6, mxy, mcol)
+    m = moved
+    for _ in range(3):
+        m = o.update_centers(lab, ix, m, S)
+        ix = r.assoc(lab, m, S, 0.6, mxy, mcol)
+    assert np.array_equal(idx2, ix)
+    assert_same(mp2[..., :7], m[..., :7], "centres of the edge-aware segmentation")

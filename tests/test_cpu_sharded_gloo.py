@@ -92,25 +92,29 @@ def _worker(rank, world, port, out_dir):
         for v, t in bufs:
             arr[v] = t.numpy().view(arr.dtype).reshape(arr[v].shape)
 
-    # this rank's frame: own views real, everything else poisoned
+    # this rank's frame: own views real, everything else poisoned.  The sequence below is mvs_frame_run's on a
+    # sharded frame (capi.cu halo_inputs / exchange_after_block_match / mvs_frame_init_state / propagate_impl).
     rgbx = np.full_like(rgbx_all, 0)
     rgbx[lo:hi] = rgbx_all[lo:hi]
     lab = np.full((V, H, W, 4), np.nan, np.float32)
     mp = np.full((V, mh, mw, 8), np.nan, np.float32)
     idx = np.zeros((V, H, W), np.uint32)
-    for v in range(lo, hi):
-        lab[v], mp[v], idx[v] = o.slic(rgbx[v], s.spixl_size, s.slic_color_weight, s.no_iter, s.enforce_connectivity)
-    # after SLIC the product ships RGBX + labels + centres and recomputes Lab of the halo views
-    exchange(rgbx); exchange(idx); exchange(mp)
     halo = sorted({v for v, src, dst in plan if dst == rank})
+    # (1) the halo views' INPUT images arrive first (sent by their owners here; the caller may upload them itself
+    #     instead, mvs_frame_set_halo_inputs) and their Lab is recomputed locally
+    exchange(rgbx)
     for v in halo:
         lab[v] = o.cvt(rgbx[v])
+    for v in range(lo, hi):
+        lab[v], mp[v], idx[v] = o.slic(rgbx[v], s.spixl_size, s.slic_color_weight, s.no_iter, s.enforce_connectivity)
+    # (2) block matching of the own views reads only Lab of the neighbours: no labels / centres needed yet
     levels = o.make_levels(s.min_disp, s.max_disp, s.inc)
     mp_clean = np.where(np.isnan(mp), np.float32(0), mp)   # boundary walks every view; poisoned centres are not used below
     rep = o.boundary(mp_clean, idx, s.spixl_size)
     own_map = o.block_match(lab, mp, rep, levels, sub, num, AW, s.bl_ratio, lo, hi)
     mp[lo:hi] = own_map[lo:hi]
-    exchange(mp)
+    # (3) ONE group after block matching: labels and centres (initial disparity included) of the halo views
+    exchange(idx); exchange(mp)
     g = np.float32(2 * float(s.gamma) ** 2)
     a = np.float32(2 * float(s.alpha) ** 2)
     gam, alp, fus, kss = o.refine_params(g, a, s.fuse, s.kernel_step, s.kernel_size // 2, s.spixl_size)
@@ -119,9 +123,14 @@ def _worker(rank, world, port, out_dir):
     poison = np.ones(V, bool)
     poison[lo:hi] = False
     st[poison] = np.nan
+    # (4) iteration 0 needs no plane exchange: the halo views' initial planes are {s7, (0, 0, 1)} of their centres
+    for v in halo:
+        st[v, ..., 0] = mp[v, ..., 7]
+        st[v, ..., 3:6] = (0.0, 0.0, 1.0)
     states = []
     for it in range(s.no_prop):
-        exchange(st)
+        if it > 0:
+            exchange(st)
         nxt = o.propagate(st, mp, idx, rep, flat, sub, num, it, AW, s.bl_ratio, gam, alp, fus, s.kernel_step // (it + 1),
                           np.float32(kss) / np.float32(it + 1), lo, hi)
         nxt[poison] = np.nan

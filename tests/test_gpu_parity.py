@@ -48,6 +48,41 @@ def test_slic_matches_oracle(ctx, oracle, W, H, S, conn):
     assert_bits_equal(mp[0], omp, "spixl_map")
 
 
+@pytest.mark.parametrize("W,H,S,conn", [(160, 96, 8, False), (141, 94, 8, True), (125, 75, 16, False), (37, 29, 8, False)])
+def test_slic_edge_aware_matches_oracle(ctx, oracle, W, H, S, conn):
+    """system_settings::edge_enable (clSLIC.cpp:86, 186-233) with the semantics pinned in DESIGN.md section 3"""
+    img = synth.voronoi_image(300 + W, W, H, sites=48)
+    lab, mp, idx, edge = mvs.slic_run(ctx, img, S=S, weight=0.6, no_iter=4, enforce_connectivity=conn, edge_enable=True,
+                                      want_edge=True)
+    olab, omp, oidx = oracle.slic_edge(img, S, 0.6, 4, conn, True)
+    assert_bits_equal(edge[0], oracle.edge_compute(olab), "edge magnitude")
+    assert_bits_equal(lab[0], olab, "lab (the edge pass must leave it intact)")
+    assert np.array_equal(idx[0], oidx), f"labels differ at {(idx[0] != oidx).sum()} pixels"
+    assert_bits_equal(mp[0], omp, "spixl_map")
+    # and the flag changes the segmentation (the test is not vacuous)
+    if W >= 100:
+        _, mp0, idx0 = mvs.slic_run(ctx, img, S=S, weight=0.6, no_iter=4, enforce_connectivity=conn)
+        assert not np.array_equal(idx0[0], idx[0])
+
+
+def test_pipeline_with_edge_enable_matches_oracle(ctx, oracle):
+    """the flag through mvs_frame_run: SLIC with edge-aware centres, then the unchanged depth stages"""
+    s = small_settings(3, 2, edge_enable=True)
+    rgbx, gt = synth.make_frame(9, 160, 96, 3, 2, bl_ratio=1.0, n_patches=5, dmin=4, dmax=14)
+    f = mvs.Frame(ctx, s, 160, 96)
+    try:
+        f.upload(mvs.BUF_RGBX, rgbx)
+        f.run()
+        idx, mp, disp = f.download(mvs.BUF_IDX), f.download(mvs.BUF_MAP), f.download(mvs.BUF_DISP)
+    finally:
+        f.close()
+    for v in range(6):
+        _, omp, oidx = oracle.slic_edge(rgbx[v], s.spixl_size, s.slic_color_weight, s.no_iter, False, True)
+        assert np.array_equal(idx[v], oidx)
+        assert_bits_equal(mp[v][..., :7], omp[..., :7], f"centres of view {v}")
+    assert np.isfinite(disp).any()
+
+
 def test_slic_stagewise(ctx, oracle):
     """one association / one update at a time, against the oracle's single kernels"""
     W, H, S = 168, 104, 8

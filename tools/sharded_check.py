@@ -35,22 +35,28 @@ def main():
     dist.broadcast_object_list(uid, src=0)
     ctx.comm_init(uid[0], world, rank)
     lo, hi = mvs.view_partition(V, world, rank)
-    part = mvs.Frame(ctx, s, W, H, lo, hi)
-    if hi > lo:
-        part.upload(mvs.BUF_RGBX, rgbx[lo:hi], lo, hi)
-    part.run()
-    part.view_fusion()
     bad = []
-    for name, which in (("labels", mvs.BUF_IDX), ("centres", mvs.BUF_MAP), ("rays", mvs.BUF_REP), ("flatness", mvs.BUF_FLAT),
+    for local_halo in (False, True):   # halo images sent by their owners / uploaded by this rank itself
+      part = mvs.Frame(ctx, s, W, H, lo, hi)
+      if hi > lo:
+        part.upload(mvs.BUF_RGBX, rgbx[lo:hi], lo, hi)
+      if local_halo:
+        for v in part.halo_views():
+            part.upload(mvs.BUF_RGBX, rgbx[v:v + 1], v, v + 1)
+        part.set_halo_inputs(True)
+      part.run()
+      part.view_fusion()
+      for name, which in (("labels", mvs.BUF_IDX), ("centres", mvs.BUF_MAP), ("rays", mvs.BUF_REP), ("flatness", mvs.BUF_FLAT),
                         ("state A", mvs.BUF_STATE_A), ("state B", mvs.BUF_STATE_B), ("disparity", mvs.BUF_DISP),
                         ("fused disparity", mvs.BUF_DISP_FUSED)):
         if hi > lo:
             a, b = part.download(which, lo, hi), whole.download(which, lo, hi)
             if not np.array_equal(np.ascontiguousarray(a).view(np.uint8), np.ascontiguousarray(b).view(np.uint8)):
-                bad.append(name)
+                bad.append(f"{name} (halo inputs {'local' if local_halo else 'exchanged'})")
+      part.close()
     flag = torch.tensor([len(bad)], device=f"cuda:{local}")
     dist.all_reduce(flag)
-    part.close(); whole.close(); ctx.close()
+    whole.close(); ctx.close()
     dist.barrier()
     dist.destroy_process_group()
     if bad:
