@@ -675,12 +675,20 @@ static int exchange_plan(int V, int nranks, const int *part, const int *view_sub
     return 0;
 }
 
+// A frame takes part in the halo exchanges when its context has a communicator of more than one rank AND it holds only
+// part of the views.  A frame that holds every view reads nothing it does not have (and in any partition that gives
+// one rank every view, all other ranks are empty and post nothing either).
+static bool sharded(const mvs_frame *f)
+{
+    return f->ctx->comm && f->ctx->nranks > 1 && !(f->lo == 0 && f->hi == f->d.V);
+}
+
 // `count` buffers go out in ONE group (one launch, one synchronisation with the neighbour ranks); transfers between
 // a pair of ranks are matched in issue order, which is the same plan order on both sides
 static int exchange_raw_multi(mvs_frame *f, int count, char *const *base, const size_t *per_view)
 {
     mvs_ctx *c = f->ctx;
-    if (!c->comm || c->nranks == 1) return 0;
+    if (!sharded(f)) return 0;
     std::vector<int> t;
     build_exchange_plan(f->d.V, c->nranks, f->part.empty() ? nullptr : f->part.data(), f->h_subset.data(),
                         f->h_subset_num.data(), t);
@@ -794,7 +802,7 @@ extern "C" int mvs_frame_slic(mvs_frame *f)
 //   * ONE group after block matching carries labels and centres (initial disparity included) of the halo views.
 static int halo_inputs(mvs_frame *f)
 {
-    if (!f->ctx->comm || f->ctx->nranks == 1) return 0;
+    if (!sharded(f)) return 0;
     CK(cudaSetDevice(f->ctx->device));
     StageTimer t(f, ST_EXCH);
     if (!f->halo_inputs_local)
@@ -807,7 +815,7 @@ static int halo_inputs(mvs_frame *f)
 
 static int exchange_after_block_match(mvs_frame *f)
 {
-    if (!f->ctx->comm || f->ctx->nranks == 1) return 0;
+    if (!sharded(f)) return 0;
     CK(cudaSetDevice(f->ctx->device));
     StageTimer t(f, ST_EXCH);
     char *base[2] = {(char *)f->d.idx, (char *)f->d.map};
@@ -874,7 +882,7 @@ extern "C" int mvs_frame_init_state(mvs_frame *f)
     StageTimer t(f, ST_INIT);
     RefineArgs a{f->gamma, f->alpha, f->fuse, f->bl_ratio, f->kernel_step, f->kss, 0};
     f->ctx->launches += launch_init_state(f->d, a, f->lo, f->hi, f->ctx->stream);
-    if (f->ctx->comm && f->ctx->nranks > 1) {
+    if (sharded(f)) {
         // the initial planes of the halo views follow from the centres this rank holds since the exchange after block
         // matching: iteration 0 needs no plane exchange
         std::vector<int> halo;
@@ -910,7 +918,7 @@ static int propagate_impl(mvs_frame *f, int iter, unsigned long long *stats_dev)
     int src = iter & 1, dst = src ^ 1;   // even: A -> B, odd: B -> A (depth_refinement.cpp:744-753)
     const bool have_halo = iter == 0 && f->halo_plane0;
     f->halo_plane0 = false;
-    if (f->ctx->comm && f->ctx->nranks > 1 && !have_halo)
+    if (sharded(f) && !have_halo)
         if (mvs_frame_exchange(f, src ? MVS_BUF_STATE_B : MVS_BUF_STATE_A)) return 1;
     if (!f->d.pixd) CK(cudaMalloc(&f->d.pixd, sizeof(uint2) * (size_t)f->d.V * f->d.N));
     StageTimer t(f, ST_PROP);
@@ -987,10 +995,10 @@ extern "C" int mvs_frame_view_fusion(mvs_frame *f)
     if (!d.disp_fused) { CK(cudaMalloc(&d.disp_fused, bytes)); }
     cudaStream_t st = f->ctx->stream;
     mvs_ctx *c = f->ctx;
-    if (c->comm && c->nranks > 1) {
-        // Every rank of the communicator takes this branch, whatever it owns, so that the transfers pair up: rank
-        // s sends its own images to rank r exactly when both hold views (a rank without views votes nothing and
-        // needs no images; a rank that owns every view still serves the others).
+    if (sharded(f)) {
+        // Transfers pair up by the partition table alone: rank s sends its own images to rank r exactly when both
+        // hold views (a rank without views votes nothing and needs no images; a rank that holds every view is not
+        // sharded, and then every other rank is empty and posts nothing).
         StageTimer t(f, ST_EXCH);
         std::vector<int> lo(c->nranks), hi(c->nranks);
         for (int r = 0; r < c->nranks; ++r) {

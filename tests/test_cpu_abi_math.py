@@ -30,8 +30,8 @@ def test_library_exports_every_declared_symbol():
 
 
 def test_params_struct_layout():
-    # mvs_params: 20 four-byte fields, no padding
-    assert C.sizeof(mvs.Params) == 80
+    # mvs_params: 21 four-byte fields (edge_enable last), no padding
+    assert C.sizeof(mvs.Params) == 84
 
 
 def test_no_cpu_fallback_without_device():
@@ -102,8 +102,13 @@ def test_pinned_exp_double_close_to_libm(oracle):
 
 
 def test_pinned_cbrt_close_to_libm(oracle):
+    """the division-free cube root: <= 1 ulp over the whole positive normal range (sampled) and over EVERY float
+    of the interval rgb2lab can feed it, exact on exact cubes"""
     rng = np.random.default_rng(3)
-    x = np.concatenate([rng.uniform(0.008856, 1.2, 200000), [0.008857, 1.0, 0.125, 8.0]]).astype(np.float32)
+    lo, hi = np.float32(0.008856).view(np.uint32), np.float32(1.2).view(np.uint32)
+    every = np.arange(int(lo), int(hi) + 1, dtype=np.uint32).view(np.float32)
+    wide = np.exp(rng.uniform(np.log(1e-37), np.log(1e37), 400000)).astype(np.float32)
+    x = np.concatenate([every, wide, np.array([0.008857, 1.0, 0.125, 8.0], np.float32)])
     y = np.empty_like(x)
     oracle.lib.orc_math_cbrtf(x.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p), len(x))
     want = np.cbrt(x.astype(np.float64)).astype(np.float32)
