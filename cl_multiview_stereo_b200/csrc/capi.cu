@@ -112,6 +112,7 @@ struct mvs_frame {
     size_t ev_used = 0;
     bool timing = false;           // per-stage CUDA events are opt-in (mvs_frame_set_timing)
     std::string timer_err;         // first failure of an event call inside a StageTimer
+    bool no_shear = false;            // the level-aligned Lab copies could not be allocated
     bool halo_inputs_local = false;   // the caller uploads the halo views' input images (mvs_frame_set_halo_inputs)
     bool halo_plane0 = false;      // plane[0] of the halo views already holds the initial state (mvs_frame_init_state)
 };
@@ -366,7 +367,7 @@ extern "C" int mvs_frame_destroy(mvs_frame *f)
     FrameDev &d = f->d;
     void *bufs[] = {d.rgbx, d.lab, d.idx, d.idx_tmp, d.map, d.rep, d.flat, d.disp, d.pixd, d.disp_proj, d.disp_fused,
                     d.io_stage, d.view_subset, d.subset_num, d.levels, d.plane[0], d.plane[1], d.cost[0], d.cost[1],
-                    d.state6[0], d.state6[1], d.edge, d.pixcol, d.spcol};
+                    d.state6[0], d.state6[1], d.edge, d.pixcol, d.spcol, d.labT, d.labSp, d.labSm};
     for (void *p : bufs) if (p) keep(cudaFree(p));
     for (cudaEvent_t e : f->ev) keep(cudaEventDestroy(e));
     delete d.bm_tma;
@@ -846,6 +847,8 @@ extern "C" int mvs_frame_halo_views(mvs_frame *f, int *views, int cap, int *coun
     return 0;
 }
 
+static void read_view_runs(mvs_frame *f, std::vector<std::pair<int, int>> &runs);
+
 extern "C" int mvs_frame_block_match(mvs_frame *f)
 {
     if (!f) return fail("null frame");
@@ -860,7 +863,30 @@ extern "C" int mvs_frame_block_match(mvs_frame *f)
         const char *why = "";
         if (prepare_block_match_tma(f->d, f->h_levels.data(), (int)f->h_levels.size(), f->bl_ratio, &why))
             return fail("block_match: tensor map: %s", why);
+        // level-aligned copies of Lab (transposed, two sheared) for every view this rank's matcher reads, unless the
+        // caller forces another kernel or the memory is not there (then the gather kernel runs)
+        static const bool other = [] { const char *e = getenv("MVS_BM_MODE"); return e && (!strcmp(e, "gather") || !strcmp(e, "tma")); }();
+        FrameDev &d = f->d;
+        if (!other && !f->no_shear) {
+            const size_t nT = sizeof(float4) * (size_t)d.V * d.N, nS = sizeof(float4) * (size_t)d.V * (d.W + d.H - 1) * d.H;
+            if (!d.labT) {
+                cudaError_t e = cudaMalloc(&d.labT, nT);
+                if (e == cudaSuccess) e = cudaMalloc(&d.labSp, nS);
+                if (e == cudaSuccess) e = cudaMalloc(&d.labSm, nS);
+                if (e != cudaSuccess) {   // not enough memory for the copies: stay with the gather kernel
+                    cudaGetLastError();
+                    cudaFree(d.labT); cudaFree(d.labSp); cudaFree(d.labSm);
+                    d.labT = d.labSp = d.labSm = nullptr;
+                    f->no_shear = true;
+                }
+            }
+        }
         StageTimer t(f, ST_BM);
+        if (d.labT && !other) {
+            std::vector<std::pair<int, int>> runs;
+            read_view_runs(f, runs);
+            for (auto &r : runs) f->ctx->launches += launch_lab_shear(d, r.first, r.second, st);
+        }
         f->ctx->launches += launch_block_match(f->d, f->bl_ratio, f->lo, f->hi, st);
     }
     return check_stage(f, "block_match");

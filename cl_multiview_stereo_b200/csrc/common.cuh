@@ -32,6 +32,9 @@ struct FrameDev {
     int M;              // mw*mh
     uchar4 *rgbx;       // [V][N]
     float4 *lab;        // [V][N]   {L,a,b,0}
+    float4 *labT;       // [V][W][H]         Lab transposed            } level-aligned copies for the block matcher
+    float4 *labSp;      // [V][W+H-1][H]     Lab sheared along x - y   } (launch_lab_shear; allocated on demand,
+    float4 *labSm;      // [V][W+H-1][H]     Lab sheared along x + y   }  photo.cu)
     uint32_t *idx;      // [V][N]
     uint32_t *idx_tmp;  // [V][N]   connectivity ping-pong (allocated on demand)
     float4 *map;        // [V][M][2] float8 {id,cx,cy,L | a,b,n,disp}
@@ -82,6 +85,7 @@ int launch_connectivity(const FrameDev &f, int z0, int z1, cudaStream_t st);
 
 int launch_boundary(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int launch_block_match(const FrameDev &f, float bl_ratio, int z0, int z1, cudaStream_t st);
+int launch_lab_shear(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int prepare_block_match_tma(const FrameDev &f, const float *levels_host, int nlev, float bl_ratio, const char **why);
 
 int launch_flatness(const FrameDev &f, float gamma_flat, int z0, int z1, cudaStream_t st);

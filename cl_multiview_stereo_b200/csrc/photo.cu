@@ -200,6 +200,169 @@ k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const ui
 }
 
 // ---------------------------------------------------------------------------------------
+// Block matching on level-aligned copies of Lab.
+//
+// With lanes = disparity levels, the 32 gathers of a warp for one sample are one contiguous run of a neighbour in the
+// SAME camera row (consecutive levels shift by one pixel along the image row: 4-5 cache lines), but 32 different image
+// rows for every other neighbour -- the reason the kernel above regroups lanes and stages terms in shared memory for
+// those pairs, and sits on the L1 tag stage (97 % busy).  Here the neighbour image is read from a copy whose memory
+// order follows the direction consecutive levels move in:
+//   same row     (dy = 0)      lab   [y][x]                row-major, as produced by cvt
+//   same column  (dx = 0)      labT  [x][y]                transposed: levels walk down a column
+//   diagonal, dx = dy          labSp [x - y + H - 1][y]    sheared + transposed: levels walk (-1, -1) per step
+//   diagonal, dx = -dy         labSm [x + y][y]
+// (bl_ratio close to 1: the row shift of level d is round-ish(bl * d), so a warp's gathers fall into two or three
+// runs; any other bl_ratio is still exact, only less aligned).  Every pair then runs the same loop: pixel address =
+// xp * KX + yp * KY + K0 with three per-neighbour constants, lanes = levels, the reference's '+30, -30' chain
+// (clcode.cl:1030-1053) per lane, no shared-memory staging of terms.  k_lab_shear makes the three copies once per
+// frame (tile through shared memory, runs along y stored coalesced).
+// ---------------------------------------------------------------------------------------
+constexpr int SH_T = 32;   // tile edge of the copy kernel
+
+__global__ void __launch_bounds__(256) k_lab_shear(const float4 *__restrict__ lab, float4 *__restrict__ labT,
+                                                   float4 *__restrict__ labSp, float4 *__restrict__ labSm, int W, int H,
+                                                   int N, size_t sh_stride, int z0)
+{
+    __shared__ float4 tile[SH_T][SH_T + 1];
+    const int z = z0 + blockIdx.z;
+    const int x0 = blockIdx.x * SH_T, y0 = blockIdx.y * SH_T;
+    const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
+    const float4 *src = lab + (size_t)z * N;
+    for (int yl = ty; yl < SH_T; yl += 8) {
+        const int x = x0 + tx, y = y0 + yl;
+        if (x < W && y < H) tile[yl][tx] = src[(size_t)y * W + x];
+    }
+    __syncthreads();
+    float4 *dT = labT + (size_t)z * N, *dP = labSp + (size_t)z * sh_stride, *dM = labSm + (size_t)z * sh_stride;
+    const int y = y0 + tx;          // lanes run along y in all three copies
+    if (y < H) {
+        for (int xl = ty; xl < SH_T; xl += 8) {
+            const int x = x0 + xl;
+            if (x < W) dT[(size_t)x * H + y] = tile[tx][xl];
+        }
+        for (int d = -(SH_T - 1) + ty; d <= SH_T - 1; d += 8) {          // diagonal x - y = const of the tile
+            const int xl = d + tx;
+            if (xl >= 0 && xl < SH_T && x0 + xl < W) dP[(size_t)(x0 - y0 + d + H - 1) * H + y] = tile[tx][xl];
+        }
+        for (int e = ty; e <= 2 * (SH_T - 1); e += 8) {                  // anti-diagonal x + y = const
+            const int xl = e - tx;
+            if (xl >= 0 && xl < SH_T && x0 + xl < W) dM[(size_t)(x0 + y0 + e) * H + y] = tile[tx][xl];
+        }
+    }
+}
+
+int launch_lab_shear(const FrameDev &f, int z0, int z1, cudaStream_t st)
+{
+    if (z1 <= z0) return 0;
+    dim3 b(32, 8), g((f.W + SH_T - 1) / SH_T, (f.H + SH_T - 1) / SH_T, z1 - z0);
+    k_lab_shear<<<g, b, 0, st>>>(f.lab, f.labT, f.labSp, f.labSm, f.W, f.H, f.N, (size_t)(f.W + f.H - 1) * f.H, z0);
+    return 1;
+}
+
+#ifndef BS_UNROLL
+#define BS_UNROLL 5
+#endif
+#ifndef BS_MINB
+#define BS_MINB 4
+#endif
+constexpr int BS_WARPS = 8;
+constexpr int BS_UN = BS_UNROLL;
+
+__global__ void __launch_bounds__(BS_WARPS * 32, BS_MINB)
+k_block_match_sh(const float4 *__restrict__ lab, const float4 *__restrict__ labT, const float4 *__restrict__ labSp,
+                 const float4 *__restrict__ labSm, float4 *__restrict__ map, const uint2 *__restrict__ rep,
+                 const float *__restrict__ levels, int disp_num, const int *__restrict__ view_subset,
+                 const int *__restrict__ subset_num, int aw, int V, int W, int H, int N, int M, int mw, int mh,
+                 float bl_ratio, int z0, int cbw, int bands)
+{
+    __shared__ float4 s_ref[BS_WARPS][25];      // Lab of the reference samples
+    __shared__ float2 s_xy[BS_WARPS][25];       // their pixel coordinates as floats (exact below 2^24)
+    const unsigned FULL = 0xffffffffu;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // grid = (blocks of a map tile, views, map tiles).  A tile is cbw superpixel columns x 2 rows; tiles are numbered
+    // band-fastest inside a column block, so that consecutive tiles (all views each) read almost the same rows of
+    // the same columns of every copy: that set -- a quarter of the image width, tile rows +- the disparity range,
+    // all views, four layouts -- fits the L2 (a full-width band does not: 42 % L2 hits, 6.3 GB of DRAM reads)
+    const int cb = blockIdx.z / bands, band = blockIdx.z - cb * bands;
+    const int t = blockIdx.x * BS_WARPS + warp;                 // superpixel inside the tile, row-major (2 rows)
+    const int gx = cb * cbw + t % cbw, gy = 2 * band + t / cbw;
+    const int z = z0 + blockIdx.y;
+    if (t >= 2 * cbw || gx >= mw || gy >= mh) return;   // whole warp leaves together
+    const int sp = gy * mw + gx;
+    const size_t mi = (size_t)z * M + sp;
+    const uint2 r = rep[mi];
+    const int d0 = r.x & 255, d1 = (r.x >> 8) & 255, d2 = (r.x >> 16) & 255, d3 = r.x >> 24;
+    const int d4 = r.y & 255, d5 = (r.y >> 8) & 255, d6 = (r.y >> 16) & 255, d7 = r.y >> 24;
+    const int bb_l = max(d0, max(d1, d2)), bb_r = max(d5, max(d6, d7));
+    const int bb_t = max(d0, max(d3, d5)), bb_b = max(d2, max(d4, d7));
+    const float stepx = fmaxf(1.0f, 0.25f * (float)(bb_l + bb_r));
+    const float stepy = fmaxf(1.0f, 0.25f * (float)(bb_t + bb_b));
+    const float4 m0 = map[2 * mi];
+    const float4 *ref_img = lab + (size_t)z * N;
+    bool ref_ok = false;
+    if (lane < 25) {
+        const int i = lane / 5 - 2, j = lane % 5 - 2;
+        const int xr = f2i(m0.y + (float)i * stepx);
+        const int yr = f2i(m0.z + (float)j * stepy);
+        ref_ok = xr >= 0 && yr >= 0 && xr < W && yr < H;
+        s_xy[warp][lane] = ref_ok ? make_float2((float)xr, (float)yr) : make_float2(0.0f, 0.0f);
+        s_ref[warp][lane] = ref_ok ? ref_img[(size_t)yr * W + xr] : make_float4(0, 0, 0, 0);
+    }
+    const unsigned vmask = __ballot_sync(FULL, ref_ok);
+    __syncwarp();
+
+    const int refx = z % aw, refy = z / aw;
+    const int ns = subset_num[z];
+    const size_t sh_stride = (size_t)(W + H - 1) * H;
+    float cost_est = 1000000.0f, disp_est = 0.0f;
+    for (int base = 0; base < disp_num; base += 32) {
+        const int dl = base + lane;
+        const bool active = dl < disp_num;
+        const float d = active ? levels[dl] : 0.0f;
+        const float bd = bl_ratio * d;
+        float min_val = 1000000.0f;
+        for (int n = 0; n < ns; n++) {
+            const int view = view_subset[V * z + n];
+            const int ix = view % aw - refx, iy = view / aw - refy;
+            const float sx = d * (float)ix, sy = bd * (float)iy;
+            // the copy whose memory order follows the level direction of this neighbour, and pixel -> element
+            const float4 *img;
+            int KX, KY, K0;
+            if (iy == 0) { img = lab + (size_t)view * N; KX = 1; KY = W; K0 = 0; }
+            else if (ix == 0) { img = labT + (size_t)view * N; KX = H; KY = 1; K0 = 0; }
+            else if ((ix > 0) == (iy > 0)) { img = labSp + (size_t)view * sh_stride; KX = H; KY = 1 - H; K0 = (H - 1) * H; }
+            else { img = labSm + (size_t)view * sh_stride; KX = H; KY = 1 + H; K0 = 0; }
+            float val = 0.0f;
+#pragma unroll BS_UN
+            for (int s = 0; s < 25; ++s) {
+                const float2 xy = s_xy[warp][s];
+                const int xp = f2i(xy.x - sx);
+                const int yp = f2i(xy.y - sy);
+                val += 30.0f;
+                if (((vmask >> s) & 1u) && (unsigned)xp < (unsigned)W && (unsigned)yp < (unsigned)H) {
+                    val -= 30.0f;
+                    const float4 cr = s_ref[warp][s];
+                    const float4 cp = img[xp * KX + yp * KY + K0];
+                    val += fabsf(cr.x - cp.x) + fabsf(cr.y - cp.y) + fabsf(cr.z - cp.z);
+                }
+            }
+            if (val < min_val) min_val = val;
+        }
+        // warp argmin over this chunk of levels, ties -> lower level index
+        float bv = active ? min_val : __int_as_float(0x7f800000);
+        int bi = dl;
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            const float ov = __shfl_xor_sync(FULL, bv, o);
+            const int oi = __shfl_xor_sync(FULL, bi, o);
+            if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (bv < cost_est) { cost_est = bv; disp_est = levels[bi]; }
+    }
+    if (lane == 0) reinterpret_cast<float *>(map + 2 * mi + 1)[3] = disp_est;
+}
+
+// ---------------------------------------------------------------------------------------
 // Block matching out of TMA-staged windows.
 //
 // The gather kernel above pushes every one of its 1.9e9 sixteen-byte samples per frame through the L1 tag stage
@@ -441,6 +604,22 @@ int launch_block_match(const FrameDev &f, float bl_ratio, int z0, int z1, cudaSt
     static const bool want_tma = [] { const char *e = getenv("MVS_BM_MODE"); return e && !strcmp(e, "tma"); }();
     if (want_tma && launch_block_match_tma(f, bl_ratio, z0, z1, st)) return 1;
     const int nblocks = (f.M + BM_WARPS - 1) / BM_WARPS;
+    // level-aligned copies of Lab present (made by launch_lab_shear for this frame): the lanes = levels kernel for all pairs
+    static const bool want_gather = [] { const char *e = getenv("MVS_BM_MODE"); return e && !strcmp(e, "gather"); }();
+    if (!want_gather && f.labT && f.labSp && f.labSm && (double)(f.W + f.H) * f.H < 2147483647.0) {
+        // column blocks of about a quarter of the map width (multiples of 8 superpixels), bands of two map rows
+        int cbw = std::max(8, ((f.mw + 3) / 4 + 7) / 8 * 8);
+        const int bands = (f.mh + 1) / 2;
+        int ncb = (f.mw + cbw - 1) / cbw;
+        if ((long long)ncb * bands > 65535) { cbw = f.mw; ncb = 1; }
+        if (bands <= 65535) {
+            dim3 g((2 * cbw + BS_WARPS - 1) / BS_WARPS, z1 - z0, ncb * bands);
+            k_block_match_sh<<<g, BS_WARPS * 32, 0, st>>>(f.lab, f.labT, f.labSp, f.labSm, f.map, f.rep, f.levels, f.num_levels,
+                                                          f.view_subset, f.subset_num, f.aw, f.V, f.W, f.H, f.N, f.M, f.mw, f.mh,
+                                                          bl_ratio, z0, cbw, bands);
+            return 1;
+        }
+    }
     int band_blocks = std::max(1, (2 * f.mw + BM_WARPS - 1) / BM_WARPS);   // two superpixel rows per band
     int bands = (nblocks + band_blocks - 1) / band_blocks;
     if (bands > 65535) { band_blocks = (nblocks + 65534) / 65535; bands = (nblocks + band_blocks - 1) / band_blocks; }

@@ -55,7 +55,6 @@ constexpr int PR_UB = 4;                    // unique planes evaluated per batch
 #endif
 constexpr int PR_SIMC = PR_COL == 1 ? PR_SIMC_SLOTS : 0;   // slots of a superpixel's colour-similarity cache
 static_assert(PR_COL != 1 || (PR_SIMC >= 16 && (PR_SIMC & (PR_SIMC - 1)) == 0), "cache slots: a power of two, at least 16");
-constexpr int PR_HP = 2;                    // planes whose smoothness products are staged at a time (phases G, H)
 
 struct PArgs {
     const float4 *map;        // [V][M][2]
@@ -79,6 +78,8 @@ struct PArgs {
     int tmax;                 // smoothness terms per superpixel at most (8 + 4K)
     int ncmax;                // candidate slots per superpixel at most (valid neighbours + far + 8 pairs)
     int nsmax;                // neighbour views per view at most (8 on a grid with neib_hor = neib_ver = 1)
+    int hp;                   // planes whose smoothness products are staged at a time (phases G, H): PR_UB when their
+                              // products fit the storage of the sample table, else 2
     unsigned mw_magic;        // ceil(2^32 / mw): label -> approximate map row for the cache hash
     unsigned long long *stats;   // optional counters {superpixels, candidates, unique planes, cache probes, cache misses}
 };
@@ -90,6 +91,8 @@ struct SpLayout {
 
 // CTA layout: float4 viewt[nsmax] (one table: every superpixel of a CTA belongs to the same view), then one
 // record of L.total bytes per superpixel
+__host__ __device__ inline int sp_hp(int tmax) { return 4 * PR_UB * (tmax + 1) <= 16 * PR_UB * 9 ? PR_UB : 2; }
+
 __host__ __device__ inline SpLayout sp_layout(int tmax, int ncmax, int nsmax)
 {
     SpLayout L;
@@ -99,7 +102,7 @@ __host__ __device__ inline SpLayout sp_layout(int tmax, int ncmax, int nsmax)
     L.cp = o;    o += 16 * ncmax;             // float4 candidate planes
     L.cc = o;    o += 8 * ncmax;              // float2 costs of the unique ones
     L.sres = o;  o += 8 * PR_UB * nsmax;      // float2 per (plane, view): {term, flags}
-    const int prod_bytes = 4 * PR_HP * (tmax + 1), sdi_bytes = 16 * PR_UB * 9;
+    const int prod_bytes = 4 * sp_hp(tmax) * (tmax + 1), sdi_bytes = 16 * PR_UB * 9;
     L.stage = o; o += ((prod_bytes > sdi_bytes ? prod_bytes : sdi_bytes) + 15) & ~15;   // sdi (E,F) then prod (G,H)
     L.simc = o;  o += 8 * PR_SIMC;            // {key, similarity} cache (PR_COL 1)
     L.cw = o;    o += 4 * ncmax;              // float acceptance weight (colour similarity to the source)
@@ -497,13 +500,14 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                 sres[u * a.nsmax + n] = make_float2(term, __int_as_float(flags));
             }
             __syncwarp();   // sdi is dead from here on: prod reuses its storage
-            // G + H, PR_HP planes at a time (their products share the storage sdi had: staging all PR_UB planes at once
-            // would make `prod` the largest array of a superpixel's record and cost a resident CTA).
+            // G + H, a.hp planes at a time: their products share the storage sdi had.  With many smoothness terms
+            // (iteration 0: 8 + 4 * 13) all PR_UB planes at once would make `prod` the largest array of a superpixel's
+            // record and cost a resident CTA: two at a time then; from iteration 1 on all four fit.
             // G: compute_smoothness products, terms spread over the octet (pooling these over the warp like the
             //    consistency items costs more in index arithmetic than it saves: 15.2 -> 15.8 ms)
             // H: ordered sums, one lane per plane: views in subset order, then the smoothness terms
-            for (int h0 = 0; __any_sync(FULL, h0 < nb); h0 += PR_HP) {
-                const int h1 = min(h0 + PR_HP, nb);
+            for (int h0 = 0; __any_sync(FULL, h0 < nb); h0 += a.hp) {
+                const int h1 = min(h0 + a.hp, nb);
                 for (int u = h0; u < h1; ++u) {
                     const float4 pl = cp[uniq[b0 + u]];
                     for (int t = l8; t < T; t += 8) {
@@ -653,6 +657,7 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     a.K = r.no_kernel_steps < 0 ? 0 : r.no_kernel_steps;
     a.kernel_step_size = r.kernel_step_size; a.iter = r.iter; a.z0 = z0;
     a.tmax = 8 + 4 * a.K;
+    a.hp = sp_hp(a.tmax);
     a.mw_magic = (unsigned)((0x100000000ULL + (unsigned)f.mw - 1) / (unsigned)f.mw);
     a.stats = stats;
     // candidate slots a superpixel can fill: 8 neighbours, the far neighbours whose offset fits the map
