@@ -138,6 +138,15 @@ def device_count():
     return n.value
 
 
+def math_eval(ctx, which, x):
+    """the device's pinned math on an array (diagnostic): 0 expf, 1 expf for x <= 0, 2 polynomial-only expf for
+    |x| < 0.3465, 3 cube root, 4 round, 5 float -> int (returned as int32)"""
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.empty_like(x)
+    check(lib().mvs_math_eval(ctx._h, int(which), _ptr(x), _ptr(y), C.c_size_t(x.size)))
+    return y.view(np.int32) if which == 5 else y
+
+
 def view_partition(V, nranks, rank):
     lo, hi = C.c_int(), C.c_int()
     check(lib().mvs_view_partition(int(V), int(nranks), int(rank), C.byref(lo), C.byref(hi)))

@@ -213,6 +213,25 @@ extern "C" int mvs_comm_init(mvs_ctx *c, const void *id128, int nranks, int rank
     return 0;
 }
 
+// the device's pinned math on host arrays (diagnostic): which = 0 expf, 1 expf for non-positive arguments, 2 the
+// polynomial-only expf for |x| < 0.3465, 3 cube root, 4 round half away from zero, 5 float -> int (bits of the int)
+extern "C" int mvs_math_eval(mvs_ctx *c, int which, const float *x, float *y, size_t n)
+{
+    if (!c || !x || !y) return fail("null argument");
+    if (which < 0 || which > 5) return fail("mvs_math_eval: unknown function %d", which);
+    CK(cudaSetDevice(c->device));
+    float *dx = nullptr, *dy = nullptr;
+    CK(cudaMalloc(&dx, sizeof(float) * std::max<size_t>(n, 1)));
+    cudaError_t e = cudaMalloc(&dy, sizeof(float) * std::max<size_t>(n, 1));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dx, x, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) { c->launches += launch_math_eval(which, dx, dy, n, c->stream); e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(y, dy, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(dx); cudaFree(dy);
+    if (e != cudaSuccess) return fail("mvs_math_eval: %s", cudaGetErrorString(e));
+    return 0;
+}
+
 extern "C" int mvs_host_alloc(void **p, size_t bytes)
 {
     CK(cudaHostAlloc(p, bytes, cudaHostAllocDefault));

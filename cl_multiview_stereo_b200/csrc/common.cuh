@@ -107,6 +107,7 @@ int launch_quantise_state(const FrameDev &f, int which, int element, uint8_t *ou
 int launch_quantise_spixl(const FrameDev &f, const float *src, int stride, int off, int mode, uint8_t *out_dev, float mn,
                           float range, int z0, int z1, cudaStream_t st);
 int launch_segmentation_lines(const FrameDev &f, uchar4 *out_dev, int z0, int z1, cudaStream_t st);
+int launch_math_eval(int which, const float *x_dev, float *y_dev, size_t n, cudaStream_t st);
 int launch_export_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
 int launch_import_state(const FrameDev &f, int which, int z0, int z1, cudaStream_t st);
 

@@ -155,7 +155,9 @@ __device__ __forceinline__ bool same_bits(const float4 &p, const float4 &q)
 // PIXD: the consistency walk gathers the per-pixel {label, plane disparity} record of k_pixel_plane and keeps the
 // colour similarities of the superpixels it meets in a small per-superpixel cache (false: the walk of the first
 // round of this kernel, label -> centre record + plane, kept for A/B measurement: MVS_PROP_MODE=legacy)
-template <bool UNIT, int MINB, bool NP, bool PIXD, bool STATS>
+// SV: fuse^2 * alpha < 0.3465, so the exp of a VISIBLE sample (|diff| < fuse) has its argument in the interval where
+// expf_pinned reduces to its polynomial (expf_pinned_small: same bits, a third of the instructions)
+template <bool UNIT, int MINB, bool NP, bool PIXD, bool STATS, bool SV>
 __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
 {
     extern __shared__ __align__(16) unsigned char pr_smem[];
@@ -399,7 +401,12 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                         for (int j = 0; j < 3; ++j)
                             if (inb[j]) {
                                 const float diff = __uint_as_float(pr[j].y) - dik[j];
-                                if (fabsf(diff) < a.fuse) { visible += expf_pinned<NP>(-diff * diff * a.alpha); vws += 1.0f; if (STATS) n_vis++; }
+                                if (fabsf(diff) < a.fuse) {
+                                    const float ea = -diff * diff * a.alpha;
+                                    visible += SV ? expf_pinned_small(ea) : expf_pinned<NP>(ea);
+                                    vws += 1.0f;
+                                    if (STATS) n_vis++;
+                                }
                                 else { if (diff != diff) visible += diff; ows += 1.0f; }
                                 float sim;
 #if PR_COL == 2
@@ -688,16 +695,20 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     // the per-pixel record path needs f.pixd (k_pixel_plane of the SAME input state) and view slots below 255
     static const bool legacy = [] { const char *e = getenv("MVS_PROP_MODE"); return e && !strcmp(e, "legacy"); }();
     const bool pixd = !legacy && f.pixd && a.nsmax < 255 && (PR_COL != 2 || f.pixcol) && (PR_COL != 0 || f.spcol);
-#define PR_LAUNCH(U, B, P, X, S)                                                                                 \
+    // visible samples: |diff| < fuse and alpha >= 0, so the exp argument lies in (-fuse^2 alpha, 0]
+    const bool sv = np && a.fuse >= 0.0f && (double)a.fuse * a.fuse * a.alpha < 0.34;
+#define PR_LAUNCH(U, B, P, X, S, SVV)                                                                            \
     do {                                                                                                         \
-        if (smem > 48 * 1024) cudaFuncSetAttribute(k_propagate<U, B, P, X, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        k_propagate<U, B, P, X, S><<<g, PR_WARPS * 32, smem, st>>>(a);                                           \
+        auto kern = k_propagate<U, B, P, X, S, SVV>;                                                             \
+        if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        kern<<<g, PR_WARPS * 32, smem, st>>>(a);                                                                 \
     } while (0)
 #define PR_PICK(U, P)                                                                                            \
     do {                                                                                                         \
-        if (!pixd) PR_LAUNCH(U, 5, P, false, false);                                                             \
-        else if (stats) PR_LAUNCH(U, PR_MINB, P, true, true);                                                          \
-        else PR_LAUNCH(U, PR_MINB, P, true, false);                                                                    \
+        if (!pixd) PR_LAUNCH(U, 5, P, false, false, false);                                                      \
+        else if (stats) PR_LAUNCH(U, PR_MINB, P, true, true, false);                                             \
+        else if (sv && P) PR_LAUNCH(U, PR_MINB, P, true, false, P);                                              \
+        else PR_LAUNCH(U, PR_MINB, P, true, false, false);                                                       \
     } while (0)
     if (!unit) { if (np) PR_PICK(false, true); else PR_PICK(false, false); }
     else if (np) PR_PICK(true, true);

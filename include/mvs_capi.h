@@ -159,6 +159,10 @@ int mvs_frame_exchange(mvs_frame *f, int which);
 /* per-stage device time (ms) of the last mvs_frame_run: slic, boundary, block_match, flatness,
  * init_state, propagate(total), fusion, exchange -- 8 floats */
 int mvs_frame_stage_ms(mvs_frame *f, float *ms8);
+/* diagnostic: the device's pinned math (csrc/mvs_math.cuh) on host arrays, for bit-for-bit comparison with the oracle's
+ * copy.  which = 0 expf, 1 expf (arguments <= 0), 2 polynomial-only expf (|x| < 0.3465), 3 cube root (x > 0),
+ * 4 round half away from zero, 5 float -> int (y holds the int's bits) */
+int mvs_math_eval(mvs_ctx *ctx, int which, const float *x, float *y, size_t n);
 /* view-sharded frame: the caller uploads the INPUT images of the halo views (the views this rank's own views read) as
  * well as its own, so that no image crosses between ranks; mvs_frame_halo_views lists them */
 int mvs_frame_set_halo_inputs(mvs_frame *f, int local);

@@ -37,6 +37,36 @@ def small_settings(aw=3, ah=2, **kw):
     return mvs.SystemSettings(**base)
 
 
+def test_device_math_equals_oracle_math_bit_for_bit(ctx, oracle):
+    """csrc/mvs_math.cuh against oracle/oracle_math.h (two separately written copies of the pinned definitions), on the
+    GPU: exp over its whole range and at the special values, the non-positive variant, the polynomial-only variant on the
+    interval it is used on (it must equal the FULL exp there), the cube root on every float rgb2lab can feed it"""
+    import ctypes as C
+    rng = np.random.default_rng(11)
+
+    def orc(fn, x, dtype=np.float32):
+        y = np.empty(x.shape, dtype)
+        getattr(oracle.lib, fn)(x.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p), len(x))
+        return y
+
+    x = np.concatenate([rng.uniform(-110, 92, 400000), rng.uniform(-1, 1, 100000),
+                        [0.0, -0.0, 88.72284, 88.7229, -104.0, -104.01, np.inf, -np.inf, np.nan, -87.4, -103.9]]).astype(np.float32)
+    assert_bits_equal(mvs.math_eval(ctx, 0, x), orc("orc_math_expf", x), "expf")
+    xn = np.concatenate([-np.abs(x[np.isfinite(x)]), [np.nan, -np.inf, -0.0]]).astype(np.float32)
+    assert_bits_equal(mvs.math_eval(ctx, 1, xn), orc("orc_math_expf", xn), "expf, non-positive arguments")
+    lo, hi = np.float32(-0.3465).view(np.uint32), np.float32(-1e-30).view(np.uint32)
+    xs = -np.arange(int(np.float32(1e-30).view(np.uint32)), int(np.float32(0.3465).view(np.uint32)), 257, dtype=np.uint32).view(np.float32)
+    xs = np.concatenate([xs, -xs, [0.0, -0.0, -0.3465, 0.3465, np.nan]]).astype(np.float32)
+    assert_bits_equal(mvs.math_eval(ctx, 2, xs), orc("orc_math_expf", xs), "polynomial-only expf on |x| < 0.3465")
+    every = np.arange(int(np.float32(0.008856).view(np.uint32)), int(np.float32(1.2).view(np.uint32)) + 1, dtype=np.uint32).view(np.float32)
+    wide = np.exp(rng.uniform(np.log(1e-37), np.log(1e37), 200000)).astype(np.float32)
+    xc = np.concatenate([every, wide])
+    assert_bits_equal(mvs.math_eval(ctx, 3, xc), orc("orc_math_cbrtf", xc), "cube root")
+    xr = np.concatenate([rng.uniform(-200, 200, 100000), [0.5, -0.5, 1.5, 2.5, -2.5, 0.49999997, 3e9, -3e9, np.nan, np.inf]]).astype(np.float32)
+    assert_bits_equal(mvs.math_eval(ctx, 4, xr), orc("orc_math_roundf", xr), "round")
+    assert np.array_equal(mvs.math_eval(ctx, 5, xr), orc("orc_math_f2i", xr, np.int32))
+
+
 @pytest.mark.parametrize("W,H,S,conn", [(160, 96, 8, False), (141, 94, 8, True), (125, 75, 16, False), (37, 29, 8, False),
                                         (200, 120, 10, True)])
 def test_slic_matches_oracle(ctx, oracle, W, H, S, conn):
