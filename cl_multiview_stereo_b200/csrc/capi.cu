@@ -403,6 +403,13 @@ static int frame_alloc(mvs_ctx *ctx, int W, int H, int S, int aw, int ah, bool n
     if (W <= 0 || H <= 0 || aw <= 0 || ah <= 0) return fail("bad geometry %dx%d array %dx%d", W, H, aw, ah);
     if (S < 6) return fail("spixl_size %d < 6 is not supported (cluster_per_line = 3S/16 would be 0, clSLIC.cpp:313)", S);
     if (W < S || H < S) return fail("image %dx%d smaller than one superpixel (%d)", W, H, S);
+    // The centre update sums pixel positions as exact integers; the reference sums them as floats through its tree
+    // (clcode.cl:584-596, 741-754).  The two agree while every partial sum is an integer below 2^24, i.e. while
+    // 9 S^2 max(W, H) < 2^24 (every combination of the named workloads: S = 8 / 16 up to 4K); beyond that the
+    // reference rounds progressively and this library would differ in the last bit, so it refuses instead.
+    if (9.0 * S * S * (double)std::max(W, H) >= 16777216.0)
+        return fail("spixl_size %d with a %dx%d image: position sums of the centre update leave the exact range "
+                    "(9 S^2 max(W,H) >= 2^24)", S, W, H);
     CK(cudaSetDevice(ctx->device));
     mvs_frame *f = new mvs_frame;
     f->ctx = ctx;

@@ -113,6 +113,16 @@ def test_pipeline_with_edge_enable_matches_oracle(ctx, oracle):
     assert np.isfinite(disp).any()
 
 
+def test_position_sums_outside_the_exact_range_are_refused(ctx):
+    """the centre update carries pixel-position sums as integers, exact (= the reference's float tree) only while
+    9 S^2 max(W, H) < 2^24; beyond that the library refuses instead of differing in the last bit"""
+    img = np.zeros((64, 1024, 4), np.uint8)
+    with pytest.raises(mvs.MvsError, match="exact range"):
+        mvs.slic_run(ctx, img, S=48)
+    lab, mp, idx = mvs.slic_run(ctx, img, S=40)       # 9 * 1600 * 1024 = 14.7e6 < 2^24: accepted
+    assert idx.shape == (1, 64, 1024)
+
+
 def test_slic_stagewise(ctx, oracle):
     """one association / one update at a time, against the oracle's single kernels"""
     W, H, S = 168, 104, 8

@@ -1,18 +1,20 @@
-# round-end evidence run on one B200: tests, smoke, bench (ours + reference arm), launch list, ncu captures
-set -x
-T=${TAG:-v10}
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_$T.log 2>&1; tail -3 gpurun_out/pytest_gpu_$T.log
-python __graft_entry__.py smoke > gpurun_out/smoke_$T.log 2>&1; tail -2 gpurun_out/smoke_$T.log
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref_$T.json 2> gpurun_out/bench_ref_$T.err
-python bench.py --steps 10 --warmup 3 > gpurun_out/bench_$T.json 2> gpurun_out/bench_$T.err
-python bench.py --workload slic_4k --steps 10 --warmup 3 > gpurun_out/bench_slic4k_$T.json 2> gpurun_out/bench_slic4k_$T.err
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r01_launches_$T.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_list.log 2>&1
-TAG=$T bash tools/ncu_frame.sh > gpurun_out/capture_frame_$T.log 2>&1
-B="python bench.py --steps 1 --warmup 3 --no-cpu"
-for k in k_propagate k_block_match; do
-  timeout 400 ncu --set full --clock-control none --import-source on -k regex:$k -s 2 -c 1 -o gpurun_out/r01_${T}_$k $B > gpurun_out/ncu_$k.log 2>&1
-  ncu -i gpurun_out/r01_${T}_$k.ncu-rep --page source --csv > gpurun_out/r01_${T}_$k.source.csv 2>/dev/null
-  ncu -i gpurun_out/r01_${T}_$k.ncu-rep --page details > gpurun_out/r01_${T}_$k.details.txt 2>/dev/null
+# round-end evidence on ONE B200: tests, smoke, bench lines (ours, reference arm, secondary workloads), launch list,
+# whole-frame ncu table.   TAG=r02_v6 bash tools/final_run.sh
+T=${TAG:-r02}
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q > gpurun_out/${T}_gpu_tests.log 2>&1; tail -3 gpurun_out/${T}_gpu_tests.log
+python __graft_entry__.py smoke > gpurun_out/${T}_smoke.log 2>&1; tail -1 gpurun_out/${T}_smoke.log
+python bench.py --steps 20 --warmup 5 > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err
+python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_bench_ref.json 2> gpurun_out/${T}_bench_ref.err
+for w in bundled_15view bundled_15view_legacy beer_garden_3x3 4x4_1080p 5x5_4k; do
+  python bench.py --workload $w --steps 10 --warmup 3 --no-cpu --no-extra > gpurun_out/${T}_bench_$w.json 2> gpurun_out/${T}_bench_$w.err
 done
-rm -f gpurun_out/r01_${T}_frame.ncu-rep
-ls -la gpurun_out | tail -12
+python bench.py --workload slic_4k --steps 10 --warmup 3 > gpurun_out/${T}_bench_slic4k.json 2> gpurun_out/${T}_bench_slic4k.err
+B="python tools/stage_time.py 15view_1080p 1"
+$B > gpurun_out/${T}_plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -s 60 -c 30 --csv --log-file gpurun_out/${T}_launches.csv $B > gpurun_out/${T}_ncu_list.log 2>&1
+timeout 1500 ncu --set full --clock-control none --launch-skip 60 --launch-count 30 -o gpurun_out/${T}_frame $B > gpurun_out/${T}_ncu_frame.log 2>&1
+ncu -i gpurun_out/${T}_frame.ncu-rep --page raw --csv > gpurun_out/${T}_frame.raw.csv 2>/dev/null
+ncu -i gpurun_out/${T}_frame.ncu-rep --page details > gpurun_out/${T}_frame.details.txt 2>/dev/null
+rm -f gpurun_out/${T}_frame.ncu-rep
+python tools/ncu_table.py gpurun_out/${T}_frame.raw.csv > gpurun_out/${T}_frame_summary.md
+ls -la gpurun_out | grep ${T} | head -30
