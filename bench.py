@@ -405,11 +405,21 @@ def run_ours(args, rank, world, local_rank):
     pin_in.array[...] = rgbx
     pin_out = [mvs.PinnedBuffer((V, H, W), np.float32) for _ in range(2)]
 
+    # The two streams interleave freely.  MVS_E2E_SERIAL=1 runs the two contexts' KERNELS one frame after the other
+    # instead (mvs_ctx_wait_event on the other context's "run queued" event), so that only copies overlap kernels:
+    # measured slower (19.10 against 18.91 ms per frame), the tails of one frame's kernels fill with the other's.
+    serial = bool(os.environ.get("MVS_E2E_SERIAL"))
+    ran = [False, False]
+
     def e2e_step(i):
         k = i & 1
         ctxs[k].sync()                      # the previous frame on this context has fully landed
         frames[k].upload(mvs.BUF_RGBX, pin_in.array, sync=False)
+        if serial and ran[1 - k]:
+            ctxs[k].wait_event(ctxs[1 - k], 8)
         frames[k].run()
+        ctxs[k].event_record(8)
+        ran[k] = True
         frames[k].download(mvs.BUF_DISP, out=pin_out[k].array, sync=False)
 
     for i in range(max(args.warmup, 2)):

@@ -28,7 +28,7 @@ class Params(C.Structure):
 # every symbol include/mvs_capi.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "mvs_last_error", "mvs_device_count", "mvs_ctx_create", "mvs_ctx_destroy", "mvs_ctx_sync",
-    "mvs_ctx_launch_count", "mvs_ctx_stream", "mvs_ctx_event_record", "mvs_ctx_event_elapsed", "mvs_comm_unique_id", "mvs_comm_init", "mvs_host_alloc",
+    "mvs_ctx_launch_count", "mvs_ctx_stream", "mvs_ctx_event_record", "mvs_ctx_event_elapsed", "mvs_ctx_wait_event", "mvs_comm_unique_id", "mvs_comm_init", "mvs_host_alloc",
     "mvs_host_free", "mvs_view_partition", "mvs_exchange_plan", "mvs_frame_create", "mvs_frame_destroy", "mvs_frame_upload",
     "mvs_frame_download", "mvs_frame_upload_async", "mvs_frame_download_async", "mvs_frame_dev_ptr",
     "mvs_frame_sizes", "mvs_frame_slic", "mvs_frame_block_match", "mvs_frame_refine", "mvs_frame_flatness",

@@ -116,6 +116,10 @@ class Context:
     def event_record(self, slot):
         check(lib().mvs_ctx_event_record(self._h, int(slot)))
 
+    def wait_event(self, other, slot):
+        """work queued on this context from now on runs after `other`'s event `slot`"""
+        check(lib().mvs_ctx_wait_event(self._h, other._h, int(slot)))
+
     def event_elapsed_ms(self, a, b):
         ms = C.c_float()
         check(lib().mvs_ctx_event_elapsed(self._h, int(a), int(b), C.byref(ms)))

@@ -183,6 +183,15 @@ extern "C" int mvs_ctx_event_record(mvs_ctx *c, int slot)
     return 0;
 }
 
+extern "C" int mvs_ctx_wait_event(mvs_ctx *c, mvs_ctx *other, int slot)
+{
+    if (!c || !other || slot < 0 || slot >= 16 || !other->user_ev[slot]) return fail("bad event slot");
+    if (c->device != other->device) return fail("mvs_ctx_wait_event: contexts on devices %d and %d", c->device, other->device);
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamWaitEvent(c->stream, other->user_ev[slot], 0));
+    return 0;
+}
+
 extern "C" int mvs_ctx_event_elapsed(mvs_ctx *c, int a, int b, float *ms)
 {
     if (!c || !ms || a < 0 || b < 0 || a >= 16 || b >= 16 || !c->user_ev[a] || !c->user_ev[b]) return fail("bad event slot");

@@ -76,6 +76,10 @@ int mvs_ctx_stream(mvs_ctx *ctx, void **stream);
 /* CUDA-event timing on that stream: record into slot 0..15, elapsed ms between two slots */
 int mvs_ctx_event_record(mvs_ctx *ctx, int slot);
 int mvs_ctx_event_elapsed(mvs_ctx *ctx, int slot_a, int slot_b, float *ms);
+/* Orders the work queued on `ctx` from now on after the event `other` recorded into `slot` (same device).  Two
+ * contexts that stream frames alternately use it to run their KERNELS one frame after the other (a frame's stages
+ * keep the L2 to themselves) while the host<->device copies of one frame overlap the kernels of the other. */
+int mvs_ctx_wait_event(mvs_ctx *ctx, mvs_ctx *other, int slot);
 /* page-locked host memory for the asynchronous copies */
 int mvs_host_alloc(void **p, size_t bytes);
 int mvs_host_free(void *p);

@@ -541,3 +541,26 @@ def test_wide_neighbourhoods_match_oracle(ctx, oracle, aw, ah, nh, nv, W, H):
         assert_bits_equal(f.download(mvs.BUF_DISP), ref["disp"], "disparity")
     finally:
         f.close()
+
+
+def test_two_contexts_ordered_by_event_give_the_same_frame(ctx, oracle):
+    """mvs_ctx_wait_event: a second context's frame queued behind the first one's (the streaming pattern of
+    INTEGRATION.md) equals the oracle too; an event that was never recorded is refused"""
+    s = small_settings(3, 3, max_disp=8)
+    rgbx, _ = synth.make_frame(11, 96, 64, 3, 3, bl_ratio=1.0, n_patches=3, dmin=1, dmax=6)
+    ref = oracle.pipeline(rgbx, s)
+    ctx2 = mvs.Context(0)
+    f1, f2 = mvs.Frame(ctx, s, 96, 64), mvs.Frame(ctx2, s, 96, 64)
+    try:
+        with pytest.raises(mvs.MvsError):
+            ctx2.wait_event(ctx, 9)              # slot 9 holds no event yet
+        f1.upload(mvs.BUF_RGBX, rgbx, sync=False)
+        f1.run()
+        ctx.event_record(9)
+        f2.upload(mvs.BUF_RGBX, rgbx, sync=False)
+        ctx2.wait_event(ctx, 9)
+        f2.run()
+        for f in (f1, f2):
+            assert_bits_equal(f.download(mvs.BUF_DISP), ref["disp"], "disparity")
+    finally:
+        f1.close(); f2.close(); ctx2.close()
