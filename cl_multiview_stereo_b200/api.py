@@ -423,6 +423,16 @@ def refine_run(ctx, mp, idx, rep, S, aw, ah, bl_ratio, subset_mat, subset_num, g
     return flat, sa, sb, disp
 
 
+VIEW_FUSION_STATIC_MAX_FLOATS = 4 << 20
+
+
+def view_fusion_static(ctx, disp_dev, fused_dev, view_count, width, height, aw, bl_ratio, fuse):
+    """mvs_view_fusion_static: the vote of view_fusion_run on DEVICE pointers (ints), allocating nothing; queued on the
+    context's stream (ctx.sync() before reading the output).  At most VIEW_FUSION_STATIC_MAX_FLOATS disparities."""
+    check(lib().mvs_view_fusion_static(ctx._h, int(view_count), int(width), int(height), int(aw), C.c_float(bl_ratio),
+                                       C.c_float(fuse), C.c_void_p(disp_dev), C.c_void_p(fused_dev)))
+
+
 def view_fusion_run(ctx, disp, aw, bl_ratio, fuse):
     """the disabled tail of clDepthRefinement::fusion (depth_refinement.cpp:1382-1451) on a stack of
     per-view disparity images [V,H,W] -> (disp_proj, disp_fused).  fuse as in system_settings."""

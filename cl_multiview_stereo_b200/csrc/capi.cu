@@ -1291,6 +1291,39 @@ extern "C" int mvs_refine_run(mvs_ctx *ctx, int width, int height, int array_wid
     return rc;
 }
 
+// The vote of mvs_view_fusion_run on device buffers, allocating nothing (include/mvs_capi.h): the scratch between the
+// two kernels is the file-scope device array of fuse.cu.
+static_assert(MVS_VIEW_FUSION_STATIC_MAX_FLOATS == VIEW_FUSION_STATIC_MAX_FLOATS, "header and kernel file agree on the limit");
+
+extern "C" int mvs_view_fusion_static(mvs_ctx *ctx, int view_count, int width, int height, int array_width,
+                                      float bl_ratio, float fuse, const float *disp_dev, float *disp_fused_dev)
+{
+    if (!ctx || !disp_dev || !disp_fused_dev) return fail("mvs_view_fusion_static: null argument");
+    if (view_count <= 0 || width <= 0 || height <= 0 || array_width <= 0) return fail("mvs_view_fusion_static: bad geometry");
+    if (view_count % array_width) return fail("view_count %d is not a multiple of array_width %d", view_count, array_width);
+    const double total = (double)view_count * width * height;
+    if (total > (double)MVS_VIEW_FUSION_STATIC_MAX_FLOATS)
+        return fail("mvs_view_fusion_static: %d views of %dx%d are %.0f disparities, the static scratch holds %u "
+                    "(use mvs_view_fusion_run or mvs_frame_view_fusion, which allocate)", view_count, width, height, total,
+                    (unsigned)MVS_VIEW_FUSION_STATIC_MAX_FLOATS);
+    CK(cudaSetDevice(ctx->device));
+    for (const void *p : {(const void *)disp_dev, (const void *)disp_fused_dev}) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, p) != cudaSuccess || (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged)) {
+            cudaGetLastError();
+            return fail("mvs_view_fusion_static: %p is not a device pointer", p);
+        }
+        if (at.type == cudaMemoryTypeDevice && at.device != ctx->device)
+            return fail("mvs_view_fusion_static: %p lives on device %d, the context on device %d", p, at.device, ctx->device);
+    }
+    const char *why = "";
+    const int nl = launch_view_fusion_static(ctx->device, ctx->stream, disp_dev, disp_fused_dev, view_count, width, height,
+                                             array_width, bl_ratio, (float)(0.5 * fuse), &why);   // depth_refinement.cpp:1328
+    if (nl < 0) return fail("mvs_view_fusion_static: %s", why);
+    ctx->launches += nl;
+    return 0;
+}
+
 extern "C" int mvs_view_fusion_run(mvs_ctx *ctx, int view_count, int width, int height, int array_width, float bl_ratio,
                                    float fuse, const float *disp, float *disp_proj, float *disp_fused)
 {

@@ -99,6 +99,10 @@ int launch_spixl_colour(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int launch_pixel_colour(const FrameDev &f, int z0, int z1, cudaStream_t st);
 int propagate_needs();
 int launch_view_fusion(const FrameDev &f, float bl_ratio, float fuse, int z0, int z1, cudaStream_t st);
+// the no-allocation variant (fuse.cu): scratch in a file-scope device array of this many floats (16 MiB)
+constexpr size_t VIEW_FUSION_STATIC_MAX_FLOATS = (size_t)4 << 20;
+int launch_view_fusion_static(int device, cudaStream_t st, const float *disp, float *fused, int V, int W, int H, int aw,
+                              float bl_ratio, float fuse, const char **why);
 int launch_ingest_bgr(const FrameDev &f, const void *bgr_dev, int z0, int z1, cudaStream_t st);
 int launch_quantise_disp(const FrameDev &f, const float *src, uint8_t *out_dev, float mn, float range, int z0, int z1,
                          cudaStream_t st);

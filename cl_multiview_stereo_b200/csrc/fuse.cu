@@ -118,4 +118,54 @@ int launch_view_fusion(const FrameDev &f, float bl_ratio, float fuse, int z0, in
     return 2;
 }
 
+// ---------------------------------------------------------------------------------------
+// The same two kernels for callers that cannot allocate (mvs_view_fusion_static, capi.cu): the chased disparities
+// -- the scratch between the two launches -- live in a file-scope device array instead of a cudaMalloc'd buffer.
+// 4 Mi floats = 16 MiB, held by every GPU that loads the library until the process exits.
+// In host code `g_fusion_scratch` is only a stand-in for the symbol, not a device address: the kernels get the
+// address cudaGetSymbolAddress returns, asked once per device with that device current.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_fusion_scratch[VIEW_FUSION_STATIC_MAX_FLOATS];
+
+static float *fusion_scratch_of(int device, const char **why)
+{
+    static float *ptr[64] = {nullptr};   // written once per device; callers of one device are ordered by its context
+    if (device < 0 || device >= 64) { *why = "device number out of range"; return nullptr; }
+    if (!ptr[device]) {
+        float *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_fusion_scratch);   // the caller made `device` current
+        if (e != cudaSuccess) { *why = cudaGetErrorString(e); return nullptr; }
+        ptr[device] = p;
+    }
+    return ptr[device];
+}
+
+// disp (all V views) -> fused, both device pointers of V*W*H floats; nothing is allocated.  0, or -1 with *why.
+int launch_view_fusion_static(int device, cudaStream_t st, const float *disp, float *fused, int V, int W, int H, int aw,
+                              float bl_ratio, float fuse, const char **why)
+{
+    const size_t total = (size_t)V * W * H;
+    if (total > VIEW_FUSION_STATIC_MAX_FLOATS) { *why = "more pixels than the static scratch holds"; return -1; }
+    const size_t smem = sizeof(float) * (size_t)V * RV_THREADS + sizeof(float2) * (size_t)V;
+    if (smem > 200 * 1024) { *why = "too many views for the vote's shared-memory staging"; return -1; }
+    float *proj = fusion_scratch_of(device, why);
+    if (!proj) return -1;
+    cudaError_t e = cudaSuccess;
+    if (smem > 48 * 1024)
+        e = cudaFuncSetAttribute(k_remove_inconsistency, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // The array keeps what the last call left.  The vote of view r reads slices 0..r, all of which the chase below
+    // writes in full, so no stale value can be read; the part in use is cleared all the same, so that the scratch
+    // starts every call exactly as the zero-filled buffer of the allocating path does.
+    if (e == cudaSuccess) e = cudaMemsetAsync(proj, 0, sizeof(float) * total, st);
+    if (e != cudaSuccess) { *why = cudaGetErrorString(e); return -1; }
+    const int N = W * H;
+    dim3 g1((N + 255) / 256, V);
+    k_project_inv<<<g1, 256, sizeof(float2) * (size_t)V, st>>>(disp, proj, W, H, N, V, aw, bl_ratio, 0);
+    dim3 g2((N + RV_THREADS - 1) / RV_THREADS, V);
+    k_remove_inconsistency<<<g2, RV_THREADS, smem, st>>>(proj, disp, fused, W, H, N, V, aw, bl_ratio, fuse, 0);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { *why = cudaGetErrorString(e); return -1; }
+    return 2;
+}
+
 } // namespace mvs

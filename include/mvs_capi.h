@@ -209,6 +209,20 @@ int mvs_refine_run(mvs_ctx *ctx, int width, int height, int array_width, int arr
 /* the disabled tail of clDepthRefinement::fusion (depth_refinement.cpp:1382-1451) on host arrays:
  * disp float[V*N] in; disp_proj / disp_fused float[V*N] out (either may be NULL).  fuse is
  * system_settings::fuse (halved internally, depth_refinement.cpp:1328). */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The computation of
+ * mvs_view_fusion_run's disp_fused, allocating nothing: disp and disp_fused are DEVICE pointers to
+ * view_count*height*width floats each (input, output; caller-owned), and the scratch between the two kernels (the
+ * chased disparities) is a file-scope device array of the library, MVS_VIEW_FUSION_STATIC_MAX_FLOATS floats = 16 MiB,
+ * which every GPU that loads the library holds until the process exits.  view_count*height*width beyond that limit is
+ * refused.  The work is queued on the context's stream and not waited for (mvs_ctx_sync).  Every call on a device
+ * shares the one array, which keeps the last call's contents (the part a call uses is cleared first): calls that
+ * overlap on the GPU -- two contexts of one device -- race; order them (mvs_ctx_wait_event) or keep to one context.
+ * No cudaMalloc / cudaFree / allocating library call on this path.  fuse as in mvs_view_fusion_run. */
+#define MVS_VIEW_FUSION_STATIC_MAX_FLOATS (4u << 20)
+int mvs_view_fusion_static(mvs_ctx *ctx, int view_count, int width, int height, int array_width, float bl_ratio,
+                           float fuse, const float *disp_dev, float *disp_fused_dev);
+
 int mvs_view_fusion_run(mvs_ctx *ctx, int view_count, int width, int height, int array_width, float bl_ratio,
                         float fuse, const float *disp, float *disp_proj, float *disp_fused);
 
