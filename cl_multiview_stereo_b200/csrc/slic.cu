@@ -414,7 +414,7 @@ __host__ __device__ constexpr UpdTile upd_tile(int S)
 // per-cluster window reduction out of the staged tile (s_lab / s_idx, row pitch t.pitch); the eight floats of a
 // centre are written by eight lanes, one component each (five of them a division: one division's worth of
 // instructions instead of five on a single lane; s7 is simply not stored)
-template <int S_T>
+template <int S_T, int NT = UPD_THREADS>
 __device__ __forceinline__ void upd_reduce(const float4 *s_lab, const uint32_t *s_idx, float4 *__restrict__ map, int S, int mw,
                                            int mh, int M, int z, int gx0, int gy0, int x0, int y0)
 {
@@ -422,7 +422,7 @@ __device__ __forceinline__ void upd_reduce(const float4 *s_lab, const uint32_t *
     const int G = (S * S * 9 + 255) / 256, cpl = S * 3 / 16;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int lx = lane & 15, lyh = lane >> 4;
-    for (int ci = warp; ci < t.tcx * t.tcy; ci += UPD_THREADS / 32) {
+    for (int ci = warp; ci < t.tcx * t.tcy; ci += NT / 32) {
         const int lcx = ci % t.tcx, lcy = ci / t.tcx;
         const int gx = gx0 + lcx, gy = gy0 + lcy;
         if (gx >= mw || gy >= mh) continue;   // warp-uniform
@@ -575,6 +575,77 @@ __global__ void __launch_bounds__(UPD_THREADS) k_update_centers_tma(const __grid
     upd_reduce<S_T>(s_lab, s_idx, map, S, mw, mh, M, z, gx0, gy0, x0, y0);
 }
 
+// The TMA-staged update as a PERSISTENT, double-buffered kernel: one CTA per SM walks the tiles of the frame (x
+// fastest, so that the CTAs of a wave work on neighbouring tiles and share their halos in L2) with two tile buffers;
+// the boxes of tile i + 1 are in flight while the warps reduce tile i.  MEASURED AND REJECTED (MVS_UPD_MODE=pipe):
+// 0.31 ms per launch against 0.24 for the one-tile kernel above with two resident CTAs, with 512 or 1024 threads --
+// the update is bound by the instructions of its pinned reduction tree (30 shuffles + 45 adds per cluster for three
+// sums, issue 63 %), not by waiting for its tile; two independent CTAs overlap their phases better than one CTA
+// whose 32 warps meet at a barrier per tile.
+// A buffer is refilled only after every thread has left it: block barrier, then fence.proxy.async by the issuing thread
+// (generic-proxy reads and the label patches before it, the TMA writes after it).
+#ifndef UPP_THREADS
+#define UPP_THREADS 1024
+#endif
+template <int S_T, int NT>
+__global__ void __launch_bounds__(NT, 1) k_update_centers_pipe(const __grid_constant__ CUtensorMap tm_lab,
+                                                               const __grid_constant__ CUtensorMap tm_idx,
+                                                               float4 *__restrict__ map, int W, int H, int mw, int mh,
+                                                               int M, int z0, int ntx, int nty, int ntiles)
+{
+    constexpr int S = S_T;
+    constexpr UpdTile t = upd_tile(S);
+    constexpr uint32_t LAB_BYTES = (uint32_t)(t.rh * t.pitch * sizeof(float4));
+    constexpr uint32_t STAGE_BYTES = (uint32_t)(t.rh * t.pitch * (sizeof(float4) + sizeof(uint32_t)));
+    static_assert(LAB_BYTES % 128 == 0 && STAGE_BYTES % 128 == 0, "TMA destinations are 128-byte aligned");
+    extern __shared__ __align__(128) unsigned char upd_smem[];
+    __shared__ __align__(8) uint64_t s_bar[2];
+    auto tile_origin = [&](int tile, int &gx0, int &gy0, int &z) {
+        const int bx = tile % ntx, r = tile / ntx;
+        gx0 = bx * t.tcx; gy0 = (r % nty) * t.tcy; z = z0 + r / nty;
+    };
+    auto issue = [&](int tile, int stage) {   // one thread
+        int gx0, gy0, z;
+        tile_origin(tile, gx0, gy0, z);
+        const int x0 = gx0 * S - S, y0 = gy0 * S - S;
+        unsigned char *dst = upd_smem + (size_t)stage * STAGE_BYTES;
+        mbar_arrive_expect_tx(&s_bar[stage], STAGE_BYTES);
+        tma_load_2d(dst, &tm_lab, 2 * x0, y0 + z * H, &s_bar[stage]);   // Lab pixels are two 8-byte elements wide
+        tma_load_2d(dst + LAB_BYTES, &tm_idx, x0, y0 + z * H, &s_bar[stage]);
+    };
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar[0], 1);
+        mbar_init(&s_bar[1], 1);
+        mbar_fence_init();
+        if ((int)blockIdx.x < ntiles) issue(blockIdx.x, 0);
+    }
+    __syncthreads();
+    int i = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++i) {
+        const int stage = i & 1, next = tile + gridDim.x;
+        if (threadIdx.x == 0 && next < ntiles) {
+            fence_proxy_async();
+            issue(next, stage ^ 1);
+        }
+        int gx0, gy0, z;
+        tile_origin(tile, gx0, gy0, z);
+        const int x0 = gx0 * S - S, y0 = gy0 * S - S;
+        const float4 *s_lab = reinterpret_cast<const float4 *>(upd_smem + (size_t)stage * STAGE_BYTES);
+        uint32_t *s_idx = reinterpret_cast<uint32_t *>(upd_smem + (size_t)stage * STAGE_BYTES + LAB_BYTES);
+        mbar_wait(&s_bar[stage], (uint32_t)((i >> 1) & 1));
+        if (x0 < 0 || y0 < 0 || x0 + t.pitch > W || y0 + t.rh > H) {   // CTA-uniform: the box leaves the image
+            for (int e = threadIdx.x; e < t.rh * t.pitch; e += NT) {
+                const int ry = e / t.pitch, rx = e - ry * t.pitch;
+                const int px = x0 + rx, py = y0 + ry;
+                if (px < 0 || px >= W || py < 0 || py >= H) s_idx[e] = 0xFFFFFFFFu;
+            }
+            __syncthreads();
+        }
+        upd_reduce<S_T, NT>(s_lab, s_idx, map, S, mw, mh, M, z, gx0, gy0, x0, y0);
+        __syncthreads();   // every thread has left this buffer: the next iteration may refill it
+    }
+}
+
 // (re)build the tensor maps of the centre update for this frame's Lab / label buffers (S = 8 tile: 80 x 48 box)
 int prepare_update_centers_tma(const FrameDev &f, const char **why)
 {
@@ -605,9 +676,25 @@ int launch_update_centers(const FrameDev &f, int z0, int z1, cudaStream_t st)
         dim3 g((f.mw + t.tcx - 1) / t.tcx, (f.mh + t.tcy - 1) / t.tcy, z1 - z0);
         // S = 8 (the shipped setting): tile staged by TMA when the frame's tensor maps could be built
         // (MVS_UPD_MODE=loads forces the load-staged kernel for A/B measurement)
+        // (MVS_UPD_MODE=pipe: the persistent double-buffered kernel, a measured rejection)
         static const bool force_loads = [] { const char *e = getenv("MVS_UPD_MODE"); return e && !strcmp(e, "loads"); }();
+        static const bool force_tile = [] { const char *e = getenv("MVS_UPD_MODE"); return !(e && !strcmp(e, "pipe")); }();
         SlicTma *tm = f.slic_tma;
-        if (S == 8 && !force_loads && tm && tm->state == 1 && tm->lab == (const void *)f.lab && tm->idx == (const void *)f.idx) {
+        const bool maps_ok = S == 8 && !force_loads && tm && tm->state == 1 && tm->lab == (const void *)f.lab && tm->idx == (const void *)f.idx;
+        if (maps_ok && !force_tile && 2 * smem + 1024 <= 227 * 1024) {
+            static int sms[64] = {0};
+            int dev = 0;
+            cudaGetDevice(&dev);
+            if (dev >= 0 && dev < 64 && !sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+            const int nsm = dev >= 0 && dev < 64 && sms[dev] > 0 ? sms[dev] : 148;
+            const int ntiles = (int)(g.x * g.y * g.z);
+            auto kern = k_update_centers_pipe<8, UPP_THREADS>;
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * smem));
+            kern<<<std::min(nsm, ntiles), UPP_THREADS, 2 * smem, st>>>(tm->map_lab, tm->map_idx, f.map, f.W, f.H, f.mw, f.mh,
+                                                                       f.M, z0, (int)g.x, (int)g.y, ntiles);
+            return 1;
+        }
+        if (maps_ok) {
             cudaFuncSetAttribute(k_update_centers_tma<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             k_update_centers_tma<8><<<g, UPD_THREADS, smem, st>>>(tm->map_lab, tm->map_idx, f.map, f.W, f.H, f.mw, f.mh, f.M, z0);
             return 1;

@@ -40,7 +40,7 @@ def main():
                       ("state_b", mvs.BUF_STATE_B), ("disp", mvs.BUF_DISP)):
         sums[nm] = hashlib.sha1(np.ascontiguousarray(f.download(which)).tobytes()).hexdigest()[:12]
     out = {"workload": name, "ms_per_frame": round(total, 4), "stage_ms": st, "sha1": sums,
-           "defs": os.environ.get("MVS_NVCC_DEFS", ""), "mode": " ".join(x for x in (os.environ.get("MVS_PROP_MODE", ""), os.environ.get("MVS_BM_MODE", "")) if x)}
+           "defs": os.environ.get("MVS_NVCC_DEFS", ""), "mode": " ".join(x for x in (os.environ.get("MVS_PROP_MODE", ""), os.environ.get("MVS_BM_MODE", ""), os.environ.get("MVS_UPD_MODE", "")) if x)}
     if os.environ.get("MVS_STATS"):
         f.slic(); f.block_match(); f.flatness(); f.init_state()
         out["propagate_stats"] = [f.propagate_stats(i) for i in range(s.no_prop)]
