@@ -450,20 +450,29 @@ def run_ours(args, rank, world, local_rank):
                   "weighted": mvs.view_partition_weighted(mvs.view_weights(sub_num), world)}
         if tables["weighted"] == tables["even"]:
             del tables["weighted"]
+        # any SET of cameras per rank (a slot order of the cameras + contiguous slot ranges), balanced by measured work
+        orders = {}
+        bal_order, bal_table = mvs.view_order_balanced(s.array_width, s.array_height, world, s.neib_hor, s.neib_ver)
+        if bal_order != list(range(V)):
+            tables["balanced"] = bal_table
+            orders["balanced"] = bal_order
         frame.set_timing(False)
         frame.upload(mvs.BUF_RGBX, rgbx); frame.run(); frame.view_fusion()     # the single-GPU result to compare with
         runs = {}
         for name, table in tables.items():
             lo, hi = table[rank]
+            order = orders.get(name, list(range(V)))      # slot -> camera
             fs = mvs.Frame(ctx, s, W, H, lo, hi)
+            if name in orders:
+                fs.set_view_order(order)
             fs.set_partition(table)
             if hi > lo:
-                fs.upload(mvs.BUF_RGBX, rgbx[lo:hi], lo, hi)
+                fs.upload(mvs.BUF_RGBX, np.ascontiguousarray(rgbx[order[lo:hi]]), lo, hi)
             # a rank ingests the camera images of the views its own views read as well (host data, like its own):
             # no image crosses between ranks
             halo = fs.halo_views()
             for v in halo:
-                fs.upload(mvs.BUF_RGBX, rgbx[v:v + 1], v, v + 1)
+                fs.upload(mvs.BUF_RGBX, rgbx[order[v]:order[v] + 1], v, v + 1)
             fs.set_halo_inputs(True)
             for _ in range(args.warmup):
                 fs.run()
@@ -482,15 +491,19 @@ def run_ours(args, rank, world, local_rank):
             fs.set_timing(False)
             # sharded result must equal the single-GPU result bit for bit on the views this rank owns
             same = True
-            fs.view_fusion()                   # every rank takes part in the exchange of the disparity images
+            checked = [mvs.BUF_DISP]
+            if name not in orders:             # multi-view fusion wants the cameras in row-major order
+                fs.view_fusion()               # every rank takes part in the exchange of the disparity images
+                checked.append(mvs.BUF_DISP_FUSED)
             if hi > lo:
-                for which in (mvs.BUF_DISP, mvs.BUF_DISP_FUSED):
+                for which in checked:
                     a = fs.download(which, lo, hi)
-                    b = frame.download(which, lo, hi)
+                    b = np.stack([frame.download(which, c, c + 1)[0] for c in order[lo:hi]])
                     same = same and bool(np.array_equal(a.view(np.uint32), b.view(np.uint32)))
             same = max_over_ranks(0.0 if same else 1.0) == 0.0
             runs[name] = {"value": 1e3 / vs_ms, "unit": "frames/s", "ms_per_step": vs_ms, "scaling": "strong",
-                          "partition": name, "views_per_rank": [b - a for a, b in table], "halo_views_rank0": len(halo),
+                          "partition": name, "views_per_rank": [b - a for a, b in table],
+                          "cameras_per_rank": [order[a:b] for a, b in table], "halo_views_rank0": len(halo),
                           "halo_inputs": "uploaded by each rank with its own views (no image exchange)",
                           "exchange_ms_rank0": st["exchange"], "stage_ms_rank0": st, "bit_identical_to_1gpu": same}
             fs.close()

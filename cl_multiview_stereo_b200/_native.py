@@ -36,7 +36,7 @@ SYMBOLS = [
     "mvs_frame_stage_ms", "mvs_frame_set_timing", "mvs_slic_run", "mvs_bm_run", "mvs_refine_run",
     "mvs_frame_view_fusion", "mvs_view_fusion_run", "mvs_frame_upload_bgr", "mvs_frame_export_u8",
     "mvs_frame_draw_segmentation", "mvs_view_partition_weighted", "mvs_exchange_plan_for", "mvs_frame_set_partition",
-    "mvs_frame_propagate_stats", "mvs_draw_segmentation_run", "mvs_slic_run_edge", "mvs_frame_set_halo_inputs", "mvs_frame_halo_views", "mvs_math_eval", "mvs_view_fusion_static",
+    "mvs_frame_propagate_stats", "mvs_draw_segmentation_run", "mvs_slic_run_edge", "mvs_frame_set_halo_inputs", "mvs_frame_halo_views", "mvs_math_eval", "mvs_view_fusion_static", "mvs_frame_set_view_order", "mvs_view_order_balanced",
 ]
 
 _lib = None

@@ -101,6 +101,8 @@ struct mvs_frame {
     int lo = 0, hi = 0;
     std::vector<int> part;         // {lo, hi} of every rank (mvs_frame_set_partition); empty = mvs_view_partition
     std::vector<int> h_subset, h_subset_num;
+    std::vector<int> h_cam_of_slot;   // camera (row-major number in the array) held by every view slot; identity by default
+    bool identity_order = true;
     std::vector<float> h_levels;
     // refinement scalars (set by prepare_refine)
     float gamma_flat = 0, gamma = 0, alpha = 0, fuse = 0, kss = 0;
@@ -300,6 +302,105 @@ extern "C" int mvs_view_partition_weighted(int V, int nranks, const int *weight,
     return 0;
 }
 
+// A slot order of the cameras (mvs_frame_set_view_order) and the contiguous slot ranges of nranks ranks such that the
+// heaviest rank is as light as a greedy assignment plus pairwise improvement makes it.  Cost of a rank = sum over its
+// cameras of (w_base + w_neighbour * neighbour views) + w_halo * (views it reads but does not own: it segments those
+// itself when the halo inputs are local).  A contiguous run of row-major views cannot separate the interior cameras
+// of a small array (5x3 over 8 ranks: views 6 and 7, eight neighbours each, share a rank); any SET of cameras can.
+// Pure host code, the same answer on every rank.  camera_of_slot: V ints; lo_hi: 2*nranks ints.
+extern "C" int mvs_view_order_balanced(int aw, int ah, int neib_hor, int neib_ver, int nranks, int w_base, int w_neighbour,
+                                       int w_halo, int *camera_of_slot, int *lo_hi)
+{
+    if (aw <= 0 || ah <= 0 || nranks <= 0 || neib_hor < 0 || neib_ver < 0 || !camera_of_slot || !lo_hi)
+        return fail("mvs_view_order_balanced: bad argument");
+    if (w_base < 0 || w_neighbour < 0 || w_halo < 0) return fail("mvs_view_order_balanced: negative weight");
+    const int V = aw * ah;
+    std::vector<std::vector<int>> nb(V);
+    for (int c = 0; c < V; ++c)
+        for (int x = c % aw - neib_hor; x <= c % aw + neib_hor; ++x)
+            for (int y = c / aw - neib_ver; y <= c / aw + neib_ver; ++y)
+                if (x >= 0 && x < aw && y >= 0 && y < ah && y * aw + x != c) nb[c].push_back(y * aw + x);
+    std::vector<int> owner(V, -1);
+    auto rank_cost = [&](int r) {
+        long long own = 0;
+        std::vector<char> read(V, 0);
+        for (int c = 0; c < V; ++c)
+            if (owner[c] == r) { own += w_base + (long long)w_neighbour * (long long)nb[c].size(); for (int q : nb[c]) read[q] = 1; }
+        long long halo = 0;
+        for (int c = 0; c < V; ++c) if (read[c] && owner[c] != r) halo += w_halo;
+        return own + halo;
+    };
+    struct Cost { long long mx; double sq; };
+    auto total = [&]() {
+        Cost t{0, 0.0};
+        for (int r = 0; r < nranks; ++r) { const long long c = rank_cost(r); t.mx = std::max(t.mx, c); t.sq += (double)c * (double)c; }
+        return t;
+    };
+    auto better = [](const Cost &a, const Cost &b) { return a.mx < b.mx || (a.mx == b.mx && a.sq < b.sq); };
+    // improvement: move one camera or swap two while that helps
+    auto improve = [&]() {
+        Cost cur = total();
+        for (int pass = 0; pass < 4 * V; ++pass) {
+            bool improved = false;
+            for (int a = 0; a < V && !improved; ++a) {
+                const int ra = owner[a];
+                for (int r = 0; r < nranks && !improved; ++r) {
+                    if (r == ra) continue;
+                    owner[a] = r;
+                    const Cost t = total();
+                    if (better(t, cur)) { cur = t; improved = true; } else owner[a] = ra;
+                }
+                for (int b = a + 1; b < V && !improved; ++b) {
+                    if (owner[b] == ra) continue;
+                    std::swap(owner[a], owner[b]);
+                    const Cost t = total();
+                    if (better(t, cur)) { cur = t; improved = true; } else std::swap(owner[a], owner[b]);
+                }
+            }
+            if (!improved) break;
+        }
+        return cur;
+    };
+    // three starts, each improved, the best kept: greedy (heaviest camera first, to the rank that ends up best), the
+    // even row-major ranges, the weighted row-major ranges
+    std::vector<int> best_owner;
+    Cost best_cost{-1, 0.0};
+    for (int start = 0; start < 3; ++start) {
+        if (start == 0) {
+            std::fill(owner.begin(), owner.end(), -1);
+            std::vector<int> order(V);
+            for (int c = 0; c < V; ++c) order[c] = c;
+            std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return nb[a].size() > nb[b].size(); });
+            for (int c : order) {
+                int best_r = 0;
+                Cost bc{-1, 0.0};
+                for (int r = 0; r < nranks; ++r) {
+                    owner[c] = r;
+                    const Cost t = total();
+                    if (bc.mx < 0 || better(t, bc)) { bc = t; best_r = r; }
+                }
+                owner[c] = best_r;
+            }
+        } else {
+            std::vector<int> lh(2 * nranks), w(V);
+            for (int c = 0; c < V; ++c) w[c] = std::max(1, w_base + w_neighbour * (int)nb[c].size());
+            if (start == 1) for (int r = 0; r < nranks; ++r) mvs_view_partition(V, nranks, r, &lh[2 * r], &lh[2 * r + 1]);
+            else if (mvs_view_partition_weighted(V, nranks, w.data(), lh.data())) return 1;
+            for (int r = 0; r < nranks; ++r) for (int c = lh[2 * r]; c < lh[2 * r + 1]; ++c) owner[c] = r;
+        }
+        const Cost c = improve();
+        if (best_cost.mx < 0 || better(c, best_cost)) { best_cost = c; best_owner = owner; }
+    }
+    owner = best_owner;
+    int s = 0;
+    for (int r = 0; r < nranks; ++r) {
+        lo_hi[2 * r] = s;
+        for (int c = 0; c < V; ++c) if (owner[c] == r) camera_of_slot[s++] = c;
+        lo_hi[2 * r + 1] = s;
+    }
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------
 // frame
 // ---------------------------------------------------------------------------------------
@@ -355,8 +456,8 @@ static int set_tables(mvs_frame *f, const int *subset, const int *subset_num, co
     for (int z = 0; z < V; ++z) f->d.max_neighbours = std::max(f->d.max_neighbours, subset_num[z]);
     for (int z = 0; z < V; ++z)
         for (int k = 0; k < subset_num[z]; ++k) {
-            const int v = subset[z * V + k], aw = f->d.aw;
-            if (abs(v % aw - z % aw) > 1 || abs(v / aw - z / aw) > 1) f->d.unit_baseline = 0;
+            const int aw = f->d.aw, cv = f->h_cam_of_slot[subset[z * V + k]], cz = f->h_cam_of_slot[z];
+            if (abs(cv % aw - cz % aw) > 1 || abs(cv / aw - cz / aw) > 1) f->d.unit_baseline = 0;
         }
     cudaStream_t st = f->ctx->stream;
     CK(cudaMemcpyAsync(f->d.view_subset, f->h_subset.data(), sizeof(int) * V * V, cudaMemcpyHostToDevice, st));
@@ -395,13 +496,28 @@ extern "C" int mvs_frame_destroy(mvs_frame *f)
     FrameDev &d = f->d;
     void *bufs[] = {d.rgbx, d.lab, d.idx, d.idx_tmp, d.map, d.rep, d.flat, d.disp, d.pixd, d.disp_proj, d.disp_fused,
                     d.io_stage, d.view_subset, d.subset_num, d.levels, d.plane[0], d.plane[1], d.cost[0], d.cost[1],
-                    d.state6[0], d.state6[1], d.edge, d.pixcol, d.spcol, d.labT, d.labSp, d.labSm};
+                    d.state6[0], d.state6[1], d.edge, d.pixcol, d.spcol, d.labT, d.labSp, d.labSm, d.cam};
     for (void *p : bufs) if (p) keep(cudaFree(p));
     for (cudaEvent_t e : f->ev) keep(cudaEventDestroy(e));
     delete d.bm_tma;
     delete d.slic_tma;
     delete f;
     if (first != cudaSuccess) return fail("mvs_frame_destroy: %s", cudaGetErrorString(first));
+    return 0;
+}
+
+// camera positions of the view slots -> device
+static int upload_cameras(mvs_frame *f)
+{
+    std::vector<int2> cam(f->d.V);
+    f->identity_order = true;
+    for (int v = 0; v < f->d.V; ++v) {
+        const int c = f->h_cam_of_slot[v];
+        cam[v] = make_int2(c % f->d.aw, c / f->d.aw);
+        if (c != v) f->identity_order = false;
+    }
+    CK(cudaMemcpyAsync(f->d.cam, cam.data(), sizeof(int2) * cam.size(), cudaMemcpyHostToDevice, f->ctx->stream));
+    CK(cudaStreamSynchronize(f->ctx->stream));
     return 0;
 }
 
@@ -452,6 +568,7 @@ static int frame_alloc(mvs_ctx *ctx, int W, int H, int S, int aw, int ah, bool n
     if (need_disp) A((void **)&d.disp, VN * 4);
     A((void **)&d.view_subset, sizeof(int) * d.V * d.V);
     A((void **)&d.subset_num, sizeof(int) * d.V);
+    A((void **)&d.cam, sizeof(int2) * d.V);
     if (e != cudaSuccess) {
         std::string why = cudaGetErrorString(e);
         cudaGetLastError();
@@ -459,8 +576,54 @@ static int frame_alloc(mvs_ctx *ctx, int W, int H, int S, int aw, int ah, bool n
         return fail("frame allocation failed after %.1f MB (%d views of %dx%d): %s", asked / 1e6, aw * ah, W, H, why.c_str());
     }
     f->lo = 0; f->hi = d.V;
+    f->h_cam_of_slot.resize(d.V);
+    for (int v = 0; v < d.V; ++v) f->h_cam_of_slot[v] = v;
+    if (upload_cameras(f)) { mvs_frame_destroy(f); return 1; }
     *out = f;
     return 0;
+}
+
+// neighbour lists of every view slot, pipeline.cpp:130-142: cameras x outer, y inner, self excluded -- in the
+// reference's order whatever slot the cameras sit in (the sums over neighbour views run in list order)
+static int neighbour_tables(mvs_frame *f, const float *levels, int nlev)
+{
+    const mvs_params *p = &f->p;
+    const int V = f->d.V, aw = p->array_width, ah = p->array_height;
+    std::vector<int> slot_of(V), sub((size_t)V * V, 0), num(V, 0);
+    for (int s = 0; s < V; ++s) slot_of[f->h_cam_of_slot[s]] = s;
+    for (int s = 0; s < V; s++) {
+        const int i = f->h_cam_of_slot[s];
+        for (int x = i % aw - p->neib_hor; x <= i % aw + p->neib_hor; x++)
+            for (int y = i / aw - p->neib_ver; y <= i / aw + p->neib_ver; y++) {
+                int indx = y * aw + x;
+                if (x >= 0 && x < aw && y >= 0 && y < ah && indx != i) sub[(size_t)s * V + num[s]++] = slot_of[indx];
+            }
+    }
+    return set_tables(f, sub.data(), num.data(), levels, nlev);
+}
+
+// Places the cameras of the array in another slot order: slot s of every per-view array (and of every view index of
+// this API: uploads, downloads, view ranges, the partition table) holds camera camera_of_slot[s], a permutation of
+// 0 .. V-1 in the row-major numbering of the array.  Lets a sharded frame give every rank ANY set of cameras as one
+// contiguous slot range (sets balanced by work, tiles of the camera grid) instead of a run of row-major neighbours.
+// Call it before the first upload.  The results of a camera are the same bits in any order; multi-view fusion, whose
+// semantics depend on the order of the slices, wants the identity order and refuses any other.
+extern "C" int mvs_frame_set_view_order(mvs_frame *f, const int *camera_of_slot)
+{
+    if (!f || !camera_of_slot) return fail("null argument");
+    if (f->p.array_width * f->p.array_height != f->d.V) return fail("mvs_frame_set_view_order: not a frame of mvs_frame_create");
+    const int V = f->d.V;
+    std::vector<char> seen(V, 0);
+    for (int s = 0; s < V; ++s) {
+        const int c = camera_of_slot[s];
+        if (c < 0 || c >= V || seen[c]) return fail("mvs_frame_set_view_order: not a permutation of the %d cameras (slot %d)", V, s);
+        seen[c] = 1;
+    }
+    CK(cudaSetDevice(f->ctx->device));
+    f->h_cam_of_slot.assign(camera_of_slot, camera_of_slot + V);
+    if (upload_cameras(f)) return 1;
+    f->halo_plane0 = false;
+    return neighbour_tables(f, nullptr, 0);
 }
 
 extern "C" int mvs_frame_create(mvs_ctx *ctx, const mvs_params *p, int view_lo, int view_hi, mvs_frame **out)
@@ -476,18 +639,10 @@ extern "C" int mvs_frame_create(mvs_ctx *ctx, const mvs_params *p, int view_lo, 
         return 1;
     f->p = *p;
     f->lo = view_lo; f->hi = view_hi;
-    // disparity levels and neighbour lists, pipeline.cpp:121-142 (x outer, y inner, self excluded)
+    // disparity levels, pipeline.cpp:121-124
     std::vector<float> lev;
     for (int i = 0; i <= (p->max_disp - p->min_disp) / p->inc; i++) lev.push_back((float)(p->min_disp + i * p->inc));
-    std::vector<int> sub((size_t)V * V, 0), num(V, 0);
-    int aw = p->array_width, ah = p->array_height;
-    for (int i = 0; i < V; i++)
-        for (int x = i % aw - p->neib_hor; x <= i % aw + p->neib_hor; x++)
-            for (int y = i / aw - p->neib_ver; y <= i / aw + p->neib_ver; y++) {
-                int indx = y * aw + x;
-                if (x >= 0 && x < aw && y >= 0 && y < ah && indx != i) sub[(size_t)i * V + num[i]++] = indx;
-            }
-    if (set_tables(f, sub.data(), num.data(), lev.data(), (int)lev.size())) { mvs_frame_destroy(f); return 1; }
+    if (neighbour_tables(f, lev.data(), (int)lev.size())) { mvs_frame_destroy(f); return 1; }
     float g = (float)(2 * pow((double)p->gamma, 2)), a = (float)(2 * pow((double)p->alpha, 2));   // pipeline.cpp:164-165
     prepare_refine(f, g, a, p->fuse, p->kernel_step, p->kernel_size / 2, p->no_prop, p->bl_ratio);
     *out = f;
@@ -1049,6 +1204,9 @@ extern "C" int mvs_frame_view_fusion(mvs_frame *f)
 {
     if (!f) return fail("null frame");
     if (!f->d.disp) return fail("frame has no disparity buffer");
+    if (!f->identity_order)
+        return fail("view fusion: the slices are chased and voted in camera order (row-major), this frame holds the "
+                    "cameras in another slot order (mvs_frame_set_view_order)");
     CK(cudaSetDevice(f->ctx->device));
     FrameDev &d = f->d;
     const size_t bytes = sizeof(float) * (size_t)d.V * d.N;

@@ -52,6 +52,8 @@ struct FrameDev {
     float4 *pixcol;     // [V][N]   {L, a, b, 0} of the pixel's superpixel (only when propagate_needs() == 2; on demand)
     float *edge;        // [V][N]   edge-aware SLIC: Sobel magnitude of Lab (edge_enable; allocated on demand)
     uint8_t *io_stage;  // [V][N][4] staging of packed BGR input / 8-bit and overlay output (allocated on demand)
+    int2 *cam;          // [V]      (x, y) of every view's camera in the array: view z sits at (z % aw, z / aw) unless
+                        //          mvs_frame_set_view_order placed the cameras in another slot order
     int *view_subset;   // [V][V]
     int *subset_num;    // [V]
     float *levels;      // [L]

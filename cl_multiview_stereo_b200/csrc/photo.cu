@@ -81,7 +81,7 @@ constexpr float BM_OUTSIDE = -1.0f;   // staged term of a sample that projects o
 __global__ void __launch_bounds__(BM_WARPS * 32, 5)
 k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const uint2 *__restrict__ rep,
               const float *__restrict__ levels, int disp_num, const int *__restrict__ view_subset,
-              const int *__restrict__ subset_num, int aw, int V, int W, int H, int N, int M, float bl_ratio, int z0,
+              const int *__restrict__ subset_num, const int2 *__restrict__ cam, int V, int W, int H, int N, int M, float bl_ratio, int z0,
               int band_blocks)
 {
     __shared__ float4 s_ref[BM_WARPS][25];      // Lab of the reference samples
@@ -118,7 +118,8 @@ k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const ui
     const unsigned vmask = __ballot_sync(FULL, ref_ok);   // bit s: reference sample s lies inside the image
     __syncwarp();
 
-    int refx = z % aw, refy = z / aw;
+    const int2 cz = cam[z];   // position of the view's camera in the array (slot order need not be row-major)
+    int refx = cz.x, refy = cz.y;
     int ns = subset_num[z];
     float cost_est = 1000000.0f, disp_est = 0.0f;
     float *t = s_t[warp];
@@ -131,7 +132,8 @@ k_block_match(const float4 *__restrict__ lab, float4 *__restrict__ map, const ui
         float min_val = 1000000.0f;
         for (int n = 0; n < ns; n++) {
             int view = view_subset[V * z + n];
-            float dx = (float)(view % aw - refx), dy = (float)(view / aw - refy);
+            const int2 cv = cam[view];
+            float dx = (float)(cv.x - refx), dy = (float)(cv.y - refy);
             const float4 *pimg = lab + (size_t)view * N;
             float val = 0.0f;
             if (dy == 0.0f) {
@@ -272,7 +274,7 @@ __global__ void __launch_bounds__(BS_WARPS * 32, BS_MINB)
 k_block_match_sh(const float4 *__restrict__ lab, const float4 *__restrict__ labT, const float4 *__restrict__ labSp,
                  const float4 *__restrict__ labSm, float4 *__restrict__ map, const uint2 *__restrict__ rep,
                  const float *__restrict__ levels, int disp_num, const int *__restrict__ view_subset,
-                 const int *__restrict__ subset_num, int aw, int V, int W, int H, int N, int M, int mw, int mh,
+                 const int *__restrict__ subset_num, const int2 *__restrict__ cam, int V, int W, int H, int N, int M, int mw, int mh,
                  float bl_ratio, int z0, int cbw, int bands)
 {
     __shared__ float4 s_ref[BS_WARPS][25];      // Lab of the reference samples
@@ -311,7 +313,8 @@ k_block_match_sh(const float4 *__restrict__ lab, const float4 *__restrict__ labT
     const unsigned vmask = __ballot_sync(FULL, ref_ok);
     __syncwarp();
 
-    const int refx = z % aw, refy = z / aw;
+    const int2 cz = cam[z];
+    const int refx = cz.x, refy = cz.y;
     const int ns = subset_num[z];
     const size_t sh_stride = (size_t)(W + H - 1) * H;
     float cost_est = 1000000.0f, disp_est = 0.0f;
@@ -323,7 +326,8 @@ k_block_match_sh(const float4 *__restrict__ lab, const float4 *__restrict__ labT
         float min_val = 1000000.0f;
         for (int n = 0; n < ns; n++) {
             const int view = view_subset[V * z + n];
-            const int ix = view % aw - refx, iy = view / aw - refy;
+            const int2 cv = cam[view];
+            const int ix = cv.x - refx, iy = cv.y - refy;
             const float sx = d * (float)ix, sy = bd * (float)iy;
             // the copy whose memory order follows the level direction of this neighbour, and pixel -> element
             const float4 *img;
@@ -388,7 +392,8 @@ struct BmTmaArgs {
     const uint2 *rep;
     const float *levels;
     const int *view_subset, *subset_num;
-    int disp_num, aw, V, W, H, N, M, mw, mh, z0;
+    const int2 *cam;
+    int disp_num, V, W, H, N, M, mw, mh, z0;
     float bl_ratio, dmin, dmax;
     int bw[3], bh[3];
 };
@@ -459,7 +464,8 @@ k_block_match_tma(const __grid_constant__ CUtensorMap tm_row, const __grid_const
     const int bx_lo = s_box[0], by_lo = s_box[2];
     const bool any_ref = s_box[1] >= s_box[0];
 
-    const int refx = z % a.aw, refy = z / a.aw;
+    const int2 cz = a.cam[z];
+    const int refx = cz.x, refy = cz.y;
     const int ns = a.subset_num[z];
     const bool active = lane < a.disp_num;
     const float d = active ? a.levels[lane] : 0.0f;
@@ -468,7 +474,8 @@ k_block_match_tma(const __grid_constant__ CUtensorMap tm_row, const __grid_const
 
     for (int n = 0; n < ns; ++n) {
         const int view = a.view_subset[a.V * z + n];
-        const int idx_x = view % a.aw - refx, idx_y = view / a.aw - refy;
+        const int2 cv = a.cam[view];
+        const int idx_x = cv.x - refx, idx_y = cv.y - refy;
         const float dx = (float)idx_x, dy = (float)idx_y;
         const int cls = idx_y == 0 ? 0 : (idx_x == 0 ? 1 : 2);
         const int BW = cls == 0 ? a.bw[0] : (cls == 1 ? a.bw[1] : a.bw[2]);
@@ -559,7 +566,7 @@ static int launch_block_match_tma(const FrameDev &f, float bl_ratio, int z0, int
     if (t->state < 0) return 0;
     BmTmaArgs a;
     a.lab = f.lab; a.map = f.map; a.rep = f.rep; a.levels = f.levels; a.view_subset = f.view_subset; a.subset_num = f.subset_num;
-    a.disp_num = f.num_levels; a.aw = f.aw; a.V = f.V; a.W = f.W; a.H = f.H; a.N = f.N; a.M = f.M; a.mw = f.mw; a.mh = f.mh;
+    a.disp_num = f.num_levels; a.cam = f.cam; a.V = f.V; a.W = f.W; a.H = f.H; a.N = f.N; a.M = f.M; a.mw = f.mw; a.mh = f.mh;
     a.z0 = z0; a.bl_ratio = bl_ratio; a.dmin = t->dmin; a.dmax = t->dmax;
     size_t smem = 0;
     for (int c = 0; c < 3; ++c) { a.bw[c] = t->bw[c]; a.bh[c] = t->bh[c]; smem = std::max(smem, (size_t)t->bw[c] * t->bh[c] * 16); }
@@ -615,7 +622,7 @@ int launch_block_match(const FrameDev &f, float bl_ratio, int z0, int z1, cudaSt
         if (bands <= 65535) {
             dim3 g((2 * cbw + BS_WARPS - 1) / BS_WARPS, z1 - z0, ncb * bands);
             k_block_match_sh<<<g, BS_WARPS * 32, 0, st>>>(f.lab, f.labT, f.labSp, f.labSm, f.map, f.rep, f.levels, f.num_levels,
-                                                          f.view_subset, f.subset_num, f.aw, f.V, f.W, f.H, f.N, f.M, f.mw, f.mh,
+                                                          f.view_subset, f.subset_num, f.cam, f.V, f.W, f.H, f.N, f.M, f.mw, f.mh,
                                                           bl_ratio, z0, cbw, bands);
             return 1;
         }
@@ -625,7 +632,7 @@ int launch_block_match(const FrameDev &f, float bl_ratio, int z0, int z1, cudaSt
     if (bands > 65535) { band_blocks = (nblocks + 65534) / 65535; bands = (nblocks + band_blocks - 1) / band_blocks; }
     dim3 g(band_blocks, z1 - z0, bands);
     k_block_match<<<g, BM_WARPS * 32, 0, st>>>(f.lab, f.map, f.rep, f.levels, f.num_levels, f.view_subset,
-                                               f.subset_num, f.aw, f.V, f.W, f.H, f.N, f.M, bl_ratio, z0, band_blocks);
+                                               f.subset_num, f.cam, f.V, f.W, f.H, f.N, f.M, bl_ratio, z0, band_blocks);
     return 1;
 }
 

@@ -70,7 +70,8 @@ struct PArgs {
     const float2 *cost_in;    // [V][M] {sm,cs}
     float4 *plane_out;
     float2 *cost_out;
-    int V, W, H, mw, mh, N, M, aw;
+    const int2 *cam;          // [V] position of every view's camera in the array
+    int V, W, H, mw, mh, N, M;
     float gamma, alpha, bl_ratio, fuse;
     int K;                    // no_kernel_steps of this iteration
     float kernel_step_size;
@@ -201,7 +202,8 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
         for (int k = l8; k < PR_SIMC; k += 8) simc[k] = 0xFFFFFFFFull;
     }
     const int ns = live ? a.subset_num[z] : 0;
-    const int camx = z % a.aw, camy = z / a.aw;
+    const int2 cz = a.cam[z];
+    const int camx = cz.x, camy = cz.y;
     const double half_fly = 0.5 * (double)fl.y;   // clcode.cl:1621 is a double expression
     const int nsw = a.subset_num[z];   // warp-uniform (ns is 0 for octets outside the map)
 
@@ -223,8 +225,9 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     if (warp == 0)
         for (int n = lane; n < nsw; n += 32) {
             int view = a.view_subset[a.V * z + n];
-            viewt[n] = make_float4(__int_as_float(view * a.N), (float)(view % a.aw - camx),
-                                   (float)(view / a.aw - camy), __int_as_float(view * a.M));
+            const int2 cv = a.cam[view];
+            viewt[n] = make_float4(__int_as_float(view * a.N), (float)(cv.x - camx), (float)(cv.y - camy),
+                                   __int_as_float(view * a.M));
         }
     __syncthreads();
 
@@ -659,7 +662,7 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     a.view_subset = f.view_subset; a.subset_num = f.subset_num;
     a.pixd = f.pixd; a.pixcol = f.pixcol; a.spcol = f.spcol;
     a.plane_in = f.plane[src]; a.cost_in = f.cost[src]; a.plane_out = f.plane[dst]; a.cost_out = f.cost[dst];
-    a.V = f.V; a.W = f.W; a.H = f.H; a.mw = f.mw; a.mh = f.mh; a.N = f.N; a.M = f.M; a.aw = f.aw;
+    a.V = f.V; a.W = f.W; a.H = f.H; a.mw = f.mw; a.mh = f.mh; a.N = f.N; a.M = f.M; a.cam = f.cam;
     a.gamma = r.gamma; a.alpha = r.alpha; a.bl_ratio = r.bl_ratio; a.fuse = r.fuse;
     a.K = r.no_kernel_steps < 0 ? 0 : r.no_kernel_steps;
     a.kernel_step_size = r.kernel_step_size; a.iter = r.iter; a.z0 = z0;

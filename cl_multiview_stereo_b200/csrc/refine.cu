@@ -22,7 +22,8 @@ struct RCtx {
     const uint2 *rep;
     const float2 *flat;
     const int *view_subset, *subset_num;
-    int V, W, H, mw, mh, N, M, aw;
+    const int2 *cam;
+    int V, W, H, mw, mh, N, M;
     float gamma, alpha, bl_ratio, fuse;
 };
 
@@ -31,7 +32,7 @@ __device__ __forceinline__ RCtx make_ctx(const FrameDev &f, const RefineArgs &a)
     RCtx c;
     c.map = f.map; c.idx = f.idx; c.rep = f.rep; c.flat = f.flat;
     c.view_subset = f.view_subset; c.subset_num = f.subset_num;
-    c.V = f.V; c.W = f.W; c.H = f.H; c.mw = f.mw; c.mh = f.mh; c.N = f.N; c.M = f.M; c.aw = f.aw;
+    c.V = f.V; c.W = f.W; c.H = f.H; c.mw = f.mw; c.mh = f.mh; c.N = f.N; c.M = f.M; c.cam = f.cam;
     c.gamma = a.gamma; c.alpha = a.alpha; c.bl_ratio = a.bl_ratio; c.fuse = a.fuse;
     return c;
 }
@@ -176,14 +177,16 @@ __global__ void __launch_bounds__(128) k_init_state(FrameDev f, RefineArgs ra, i
     // ---- initialize_consistency (clcode.cl:1260-1357)
     float consistency = 0.0f;
     int view_counter = 0;
-    int camx = z % c.aw, camy = z / c.aw;
+    const int2 camz = c.cam[z];
+    int camx = camz.x, camy = camz.y;
     Samples ss = rep_samples(c.rep[id]);
     int icx = f2i(ma.y), icy = f2i(ma.z);
     int ns = c.subset_num[z];
     for (int n = 0; n < ns; n++) {
         int view = c.view_subset[z * c.V + n];
-        float rx = round_haz(d * (float)(view % c.aw - camx));
-        float ry = round_haz(c.bl_ratio * d * (float)(view / c.aw - camy));
+        const int2 cv = c.cam[view];
+        float rx = round_haz(d * (float)(cv.x - camx));
+        float ry = round_haz(c.bl_ratio * d * (float)(cv.y - camy));
         const uint32_t *vidx = c.idx + (size_t)view * c.N;
         const float4 *pm = c.map + 2 * (size_t)view * c.M;
         float vws = 0.0f, ows = 0.0f, num = 0.0f, visibility = 0.0f, visible = 0.0f;

@@ -108,6 +108,17 @@ int mvs_exchange_plan_for(int V, int nranks, const int *lo_hi, const int *view_s
  * buffers for every view are allocated because neighbour views are read (clcode.cl:1046,1314,1581). */
 int mvs_frame_create(mvs_ctx *ctx, const mvs_params *p, int view_lo, int view_hi, mvs_frame **out);
 int mvs_frame_destroy(mvs_frame *f);
+/* The cameras of the array in another SLOT order: slot s of every per-view array, and of every view index of this
+ * API (uploads, downloads, view ranges, the partition table), holds camera camera_of_slot[s] -- a permutation of
+ * 0..V-1 in the row-major numbering pipeline.cpp:130-142 uses.  Neighbour lists keep the reference's order per camera,
+ * so a camera's results are the same bits in any order.  Lets a sharded frame give a rank ANY set of cameras as one
+ * contiguous slot range.  Call before the first upload; mvs_frame_view_fusion refuses a frame in non-identity order.
+ * mvs_view_order_balanced proposes an order and the ranks' slot ranges {lo_0,hi_0,...} for nranks ranks, minimising the
+ * heaviest rank under cost = sum over own cameras (w_base + w_neighbour * neighbour views) + w_halo * views read but
+ * not owned.  Pure host code; no counterpart in the reference (single device). */
+int mvs_frame_set_view_order(mvs_frame *f, const int *camera_of_slot);
+int mvs_view_order_balanced(int array_width, int array_height, int neib_hor, int neib_ver, int nranks, int w_base,
+                            int w_neighbour, int w_halo, int *camera_of_slot, int *lo_hi);
 /* view ranges of all ranks when they are not mvs_view_partition's: same table on every rank, this rank's entry
  * must be the [view_lo,view_hi) the frame was created with.  Pure host call. */
 int mvs_frame_set_partition(mvs_frame *f, int nranks, const int *lo_hi);

@@ -199,3 +199,35 @@ def test_weighted_view_partition_minimises_the_heaviest_rank():
         mvs.view_partition_weighted([3, 0, 2], 2)
     with pytest.raises(mvs.MvsError):
         mvs.exchange_plan(4, 2, *mvs.make_subsets(2, 2), parts=[(0, 3), (2, 4)])
+
+
+def test_balanced_view_order_is_a_permutation_and_beats_contiguous_ranges():
+    """mvs_view_order_balanced: a permutation of the cameras with contiguous slot ranges; under its own cost model the
+    heaviest rank is never heavier than with the row-major even or weighted ranges, and strictly lighter on the
+    15-view array over 8 ranks (where a contiguous run cannot separate the interior cameras)"""
+    wb, wn, wh = 19, 20, 16
+
+    def cost(sets, sub, num):
+        worst = 0
+        for cams in sets:
+            own = sum(wb + wn * int(num[c]) for c in cams)
+            read = {int(sub[c, k]) for c in cams for k in range(num[c])} - set(cams)
+            worst = max(worst, own + wh * len(read))
+        return worst
+
+    for aw, ah, nh, nv in ((5, 3, 1, 1), (4, 4, 1, 1), (5, 5, 1, 1), (3, 3, 2, 1), (7, 1, 1, 1), (2, 2, 1, 1)):
+        V = aw * ah
+        sub, num = mvs.make_subsets(aw, ah, nh, nv)
+        for n in (1, 2, 3, 4, 8):
+            order, parts = mvs.view_order_balanced(aw, ah, n, nh, nv, wb, wn, wh)
+            assert sorted(order) == list(range(V))
+            assert parts[0][0] == 0 and parts[-1][1] == V and all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
+            assert (order, parts) == mvs.view_order_balanced(aw, ah, n, nh, nv, wb, wn, wh)      # deterministic
+            mine = cost([order[lo:hi] for lo, hi in parts], sub, num)
+            even = cost([list(range(*mvs.view_partition(V, n, r))) for r in range(n)], sub, num)
+            wtd = cost([list(range(lo, hi)) for lo, hi in mvs.view_partition_weighted(mvs.view_weights(num, wb, wn), n)], sub, num)
+            assert mine <= min(even, wtd), (aw, ah, n, mine, even, wtd)
+            if (aw, ah, n) == (5, 3, 8):
+                assert mine < 0.9 * min(even, wtd)
+    with pytest.raises(mvs.MvsError):
+        mvs.view_order_balanced(5, 3, 0)

@@ -543,6 +543,37 @@ def test_wide_neighbourhoods_match_oracle(ctx, oracle, aw, ah, nh, nv, W, H):
         f.close()
 
 
+@pytest.mark.parametrize("aw,ah,nh,nv", [(3, 3, 1, 1), (4, 2, 2, 1)])
+def test_any_slot_order_of_the_cameras_gives_the_same_bits_per_camera(ctx, aw, ah, nh, nv):
+    """mvs_frame_set_view_order: every buffer of a camera is bit-identical whatever slot the camera sits in (neighbour
+    lists keep the reference's order); multi-view fusion refuses a permuted frame; a non-permutation is refused"""
+    W, H, V = 96, 64, aw * ah
+    s = small_settings(aw, ah, neib_hor=nh, neib_ver=nv, max_disp=8)
+    rgbx, _ = synth.make_frame(17, W, H, aw, ah, bl_ratio=1.0, n_patches=3, dmin=1, dmax=6)
+    order = [int(c) for c in np.random.default_rng(5).permutation(V)]
+    assert order != sorted(order)
+    f0, f1 = mvs.Frame(ctx, s, W, H), mvs.Frame(ctx, s, W, H)
+    try:
+        with pytest.raises(mvs.MvsError):
+            f1.set_view_order([0] * V)
+        f1.set_view_order(order)
+        f0.upload(mvs.BUF_RGBX, rgbx)
+        f1.upload(mvs.BUF_RGBX, rgbx[order])
+        f0.run(); f1.run()
+        for which, name in ((mvs.BUF_IDX, "labels"), (mvs.BUF_MAP, "map"), (mvs.BUF_REP, "rays"), (mvs.BUF_FLAT, "flatness"),
+                            (mvs.BUF_STATE_A, "state A"), (mvs.BUF_STATE_B, "state B"), (mvs.BUF_DISP, "disparity")):
+            a, b = f0.download(which), f1.download(which)
+            assert np.array_equal(np.ascontiguousarray(a[order]).view(np.uint8), np.ascontiguousarray(b).view(np.uint8)), name
+        with pytest.raises(mvs.MvsError, match="slot order"):
+            f1.view_fusion()
+        f1.set_view_order(list(range(V)))          # back to row-major: fusion is allowed again
+        f1.upload(mvs.BUF_RGBX, rgbx)
+        f1.run(); f1.view_fusion(); f0.view_fusion()
+        assert np.array_equal(f0.download(mvs.BUF_DISP_FUSED).view(np.uint32), f1.download(mvs.BUF_DISP_FUSED).view(np.uint32))
+    finally:
+        f0.close(); f1.close()
+
+
 def test_two_contexts_ordered_by_event_give_the_same_frame(ctx, oracle):
     """mvs_ctx_wait_event: a second context's frame queued behind the first one's (the streaming pattern of
     INTEGRATION.md) equals the oracle too; an event that was never recorded is refused"""

@@ -34,26 +34,39 @@ def main():
     uid = [mvs.Context.unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     ctx.comm_init(uid[0], world, rank)
-    lo, hi = mvs.view_partition(V, world, rank)
     bad = []
-    for local_halo in (False, True):   # halo images sent by their owners / uploaded by this rank itself
+    # (halo images sent by their owners | uploaded by this rank itself) x (row-major view ranges | camera sets in a
+    # balanced slot order, which has no multi-view fusion)
+    border, btable = mvs.view_order_balanced(s.array_width, s.array_height, world, w_halo=40)
+    if border == list(range(V)):       # make sure a non-trivial order is exercised
+        border = border[::-1]
+    for local_halo, order, table in ((False, None, None), (True, None, None), (False, border, btable), (True, border, btable)):
+      lo, hi = table[rank] if table else mvs.view_partition(V, world, rank)
+      cams = order if order else list(range(V))          # slot -> camera
       part = mvs.Frame(ctx, s, W, H, lo, hi)
+      if order:
+        part.set_view_order(order)
+        part.set_partition(table)
       if hi > lo:
-        part.upload(mvs.BUF_RGBX, rgbx[lo:hi], lo, hi)
+        part.upload(mvs.BUF_RGBX, np.ascontiguousarray(rgbx[cams[lo:hi]]), lo, hi)
       if local_halo:
         for v in part.halo_views():
-            part.upload(mvs.BUF_RGBX, rgbx[v:v + 1], v, v + 1)
+            part.upload(mvs.BUF_RGBX, rgbx[cams[v]:cams[v] + 1], v, v + 1)
         part.set_halo_inputs(True)
       part.run()
-      part.view_fusion()
-      for name, which in (("labels", mvs.BUF_IDX), ("centres", mvs.BUF_MAP), ("rays", mvs.BUF_REP), ("flatness", mvs.BUF_FLAT),
-                        ("state A", mvs.BUF_STATE_A), ("state B", mvs.BUF_STATE_B), ("disparity", mvs.BUF_DISP),
-                        ("fused disparity", mvs.BUF_DISP_FUSED)):
+      bufs = [("labels", mvs.BUF_IDX), ("centres", mvs.BUF_MAP), ("rays", mvs.BUF_REP), ("flatness", mvs.BUF_FLAT),
+              ("state A", mvs.BUF_STATE_A), ("state B", mvs.BUF_STATE_B), ("disparity", mvs.BUF_DISP)]
+      if not order:
+        part.view_fusion()
+        bufs.append(("fused disparity", mvs.BUF_DISP_FUSED))
+      for name, which in bufs:
         if hi > lo:
-            a, b = part.download(which, lo, hi), whole.download(which, lo, hi)
+            a = part.download(which, lo, hi)
+            b = np.stack([whole.download(which, c, c + 1)[0] for c in cams[lo:hi]])
             if not np.array_equal(np.ascontiguousarray(a).view(np.uint8), np.ascontiguousarray(b).view(np.uint8)):
-                bad.append(f"{name} (halo inputs {'local' if local_halo else 'exchanged'})")
+                bad.append(f"{name} (halo inputs {'local' if local_halo else 'exchanged'}, {'balanced order' if order else 'row-major'})")
       part.close()
+    lo, hi = mvs.view_partition(V, world, rank)
     flag = torch.tensor([len(bad)], device=f"cuda:{local}")
     dist.all_reduce(flag)
     whole.close(); ctx.close()
