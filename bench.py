@@ -452,7 +452,8 @@ def run_ours(args, rank, world, local_rank):
             del tables["weighted"]
         # any SET of cameras per rank (a slot order of the cameras + contiguous slot ranges), balanced by measured work
         orders = {}
-        bal_order, bal_table = mvs.view_order_balanced(s.array_width, s.array_height, world, s.neib_hor, s.neib_ver)
+        bal_order, bal_table = mvs.view_order_balanced(s.array_width, s.array_height, world, s.neib_hor, s.neib_ver,
+                                                       w_halo=int(os.environ.get("MVS_W_HALO", "4")))
         if bal_order != list(range(V)):
             tables["balanced"] = bal_table
             orders["balanced"] = bal_order
@@ -489,6 +490,8 @@ def run_ours(args, rank, world, local_rank):
                 fs.run()
             st = {k: v / min(args.steps, 5) for k, v in fs.stage_ms().items()}
             fs.set_timing(False)
+            per_rank = [None] * world
+            dist.all_gather_object(per_rank, {k: round(v, 3) for k, v in st.items()})
             # sharded result must equal the single-GPU result bit for bit on the views this rank owns
             same = True
             checked = [mvs.BUF_DISP]
@@ -505,7 +508,11 @@ def run_ours(args, rank, world, local_rank):
                           "partition": name, "views_per_rank": [b - a for a, b in table],
                           "cameras_per_rank": [order[a:b] for a, b in table], "halo_views_rank0": len(halo),
                           "halo_inputs": "uploaded by each rank with its own views (no image exchange)",
-                          "exchange_ms_rank0": st["exchange"], "stage_ms_rank0": st, "bit_identical_to_1gpu": same}
+                          "exchange_ms_rank0": st["exchange"], "stage_ms_rank0": st,
+                          # per rank: time in its own kernels, and in the exchanges (transfers + waiting for its peers)
+                          "compute_ms_per_rank": [round(sum(v for k, v in r.items() if k != "exchange"), 3) for r in per_rank],
+                          "exchange_ms_per_rank": [r["exchange"] for r in per_rank],
+                          "bit_identical_to_1gpu": same}
             fs.close()
             barrier()
         best = min(runs, key=lambda k: runs[k]["ms_per_step"])

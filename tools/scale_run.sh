@@ -10,7 +10,7 @@ import json
 try:
     d=json.load(open("gpurun_out/${T}_scale_${w}_n${N}.json"))
     vs=d.get("view_sharded") or {}
-    print("$w N=$N value %.2f e2e %.2f | sharded %.3f ms exch %.3f identical %s" % (d["value"], d["e2e"]["value"], vs.get("ms_per_step",0), vs.get("exchange_ms_rank0",0), vs.get("bit_identical_to_1gpu")))
+    print("$w N=$N value %.2f e2e %.2f | sharded %.3f ms (%s) exch %.3f identical %s others %s" % (d["value"], d["e2e"]["value"], vs.get("ms_per_step",0), vs.get("partition"), vs.get("exchange_ms_rank0",0), vs.get("bit_identical_to_1gpu"), {k: (round(o["ms_per_step"],3), o["bit_identical_to_1gpu"]) for k, o in (vs.get("other_partition") or {}).items()}))
 except Exception as e:
     print("$w N=$N failed:", e); print(open("gpurun_out/${T}_scale_${w}_n${N}.err").read()[-800:])
 PY
