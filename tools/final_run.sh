@@ -1,5 +1,5 @@
 # round-end evidence on ONE B200: tests, smoke, bench lines (ours, reference arm, secondary workloads), launch list,
-# whole-frame ncu table.   TAG=r02_v6 bash tools/final_run.sh
+# whole-frame ncu table.   TAG=r02_v6 bash tools/final_run.sh   (NO_NCU=1 stops before the two ncu passes)
 T=${TAG:-r02}
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_gpu_tests.log 2>&1; tail -3 gpurun_out/${T}_gpu_tests.log
@@ -10,6 +10,7 @@ for w in bundled_15view bundled_15view_legacy beer_garden_3x3 4x4_1080p 5x5_4k; 
   python bench.py --workload $w --steps 10 --warmup 3 --no-cpu --no-extra > gpurun_out/${T}_bench_$w.json 2> gpurun_out/${T}_bench_$w.err
 done
 python bench.py --workload slic_4k --steps 10 --warmup 3 > gpurun_out/${T}_bench_slic4k.json 2> gpurun_out/${T}_bench_slic4k.err
+if [ -n "$NO_NCU" ]; then ls -la gpurun_out | grep ${T} | head -30; exit 0; fi
 B="python tools/stage_time.py 15view_1080p 1"
 $B > gpurun_out/${T}_plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -s 60 -c 30 --csv --log-file gpurun_out/${T}_launches.csv $B > gpurun_out/${T}_ncu_list.log 2>&1
 timeout 1500 ncu --set full --clock-control none --launch-skip 60 --launch-count 30 -o gpurun_out/${T}_frame $B > gpurun_out/${T}_ncu_frame.log 2>&1
