@@ -343,7 +343,7 @@ class Frame:
         """one propagate iteration with work counters (diagnostic)"""
         st = (C.c_ulonglong * 12)()
         check(lib().mvs_frame_propagate_stats(self._h, int(it), st))
-        return dict(zip(("superpixels", "candidates", "unique_planes", "cache_probes", "cache_misses", "items",
+        return dict(zip(("superpixels", "candidates", "unique_planes", "retired_3", "retired_4", "items",
                          "items_inside", "items_visible", "samples_inside", "samples_visible"), [int(x) for x in st]))
 
     def fusion(self):

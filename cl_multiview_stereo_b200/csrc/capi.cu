@@ -496,7 +496,7 @@ extern "C" int mvs_frame_destroy(mvs_frame *f)
     FrameDev &d = f->d;
     void *bufs[] = {d.rgbx, d.lab, d.idx, d.idx_tmp, d.map, d.rep, d.flat, d.disp, d.pixd, d.disp_proj, d.disp_fused,
                     d.io_stage, d.view_subset, d.subset_num, d.levels, d.plane[0], d.plane[1], d.cost[0], d.cost[1],
-                    d.state6[0], d.state6[1], d.edge, d.pixcol, d.spcol, d.labT, d.labSp, d.labSm, d.cam};
+                    d.state6[0], d.state6[1], d.edge, d.spcol, d.labT, d.labSp, d.labSm, d.cam};
     for (void *p : bufs) if (p) keep(cudaFree(p));
     for (cudaEvent_t e : f->ev) keep(cudaEventDestroy(e));
     delete d.bm_tma;
@@ -1145,10 +1145,6 @@ static int propagate_impl(mvs_frame *f, int iter, unsigned long long *stats_dev)
         if (!f->d.spcol) CK(cudaMalloc(&f->d.spcol, sizeof(float4) * (size_t)f->d.V * f->d.M));
         for (auto &r : runs) f->ctx->launches += launch_spixl_colour(f->d, r.first, r.second, f->ctx->stream);
     }
-    if (propagate_needs() == 2 && (iter == 0 || !f->d.pixcol)) {   // colours are fixed from block matching on
-        if (!f->d.pixcol) CK(cudaMalloc(&f->d.pixcol, sizeof(float4) * (size_t)f->d.V * f->d.N));
-        for (auto &r : runs) f->ctx->launches += launch_pixel_colour(f->d, r.first, r.second, f->ctx->stream);
-    }
     for (auto &r : runs) f->ctx->launches += launch_pixel_plane(f->d, src, r.first, r.second, f->ctx->stream);
     // per-iteration arguments, depth_refinement.cpp:768-769 (int / int, float / int)
     RefineArgs a{f->gamma, f->alpha, f->fuse, f->bl_ratio, f->kernel_step / (iter + 1), f->kss / (float)(iter + 1), iter};
@@ -1164,7 +1160,7 @@ static int propagate_impl(mvs_frame *f, int iter, unsigned long long *stats_dev)
 extern "C" int mvs_frame_propagate(mvs_frame *f, int iter) { return propagate_impl(f, iter, nullptr); }
 
 // One propagate iteration with work counters (a diagnostic, not part of mvs_frame_run): stats12 =
-// {superpixels, candidate planes, unique planes evaluated, similarity-cache probes, cache misses, (plane, view)
+// {superpixels, candidate planes, unique planes evaluated, 0, 0 (two retired counters), (plane, view)
 // items, items with samples inside the neighbour image, items with a visible sample, samples inside, samples visible}.
 // How many of a superpixel's candidates are bit-identical duplicates depends on the scene; the bench
 // line reports it so that a frame rate can be read against the work it stands for.

@@ -49,7 +49,6 @@ struct FrameDev {
     float *disp_proj;   // [V][N]   multi-view fusion: chased disparity (allocated on demand)
     float *disp_fused;  // [V][N]   multi-view fusion: voted disparity (allocated on demand)
     float4 *spcol;      // [V][M]   {L, a, b, 0} per superpixel, packed from map after block matching (allocated on demand)
-    float4 *pixcol;     // [V][N]   {L, a, b, 0} of the pixel's superpixel (only when propagate_needs() == 2; on demand)
     float *edge;        // [V][N]   edge-aware SLIC: Sobel magnitude of Lab (edge_enable; allocated on demand)
     uint8_t *io_stage;  // [V][N][4] staging of packed BGR input / 8-bit and overlay output (allocated on demand)
     int2 *cam;          // [V]      (x, y) of every view's camera in the array: view z sits at (z % aw, z / aw) unless
@@ -98,8 +97,6 @@ int launch_propagate(const FrameDev &f, const RefineArgs &a, int src, int dst, i
 int launch_spixl_to_image(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);
 int launch_pixel_plane(const FrameDev &f, int src, int z0, int z1, cudaStream_t st);
 int launch_spixl_colour(const FrameDev &f, int z0, int z1, cudaStream_t st);
-int launch_pixel_colour(const FrameDev &f, int z0, int z1, cudaStream_t st);
-int propagate_needs();
 int launch_view_fusion(const FrameDev &f, float bl_ratio, float fuse, int z0, int z1, cudaStream_t st);
 // the no-allocation variant (fuse.cu): scratch in a file-scope device array of this many floats (16 MiB)
 constexpr size_t VIEW_FUSION_STATIC_MAX_FLOATS = (size_t)4 << 20;

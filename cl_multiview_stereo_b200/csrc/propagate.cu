@@ -40,21 +40,13 @@ constexpr int PR_WARPS = 4;                 // warps per CTA (tile rows)
 constexpr int PR_OCT = 4;                   // octets per warp (tile columns)
 constexpr int PR_SPB = PR_WARPS * PR_OCT;   // superpixels per CTA
 constexpr int PR_UB = 4;                    // unique planes evaluated per batch
-// build-time knobs (MVS_NVCC_DEFS): resident CTAs the register allocation aims for; where the colour of the
-// superpixel under a projected sample comes from (PR_COL 0: the 32-byte centre record of the label the pixel
-// record carries, a dependent gather; 1: that gather behind a per-superpixel cache of similarities, kept as a
-// measured rejection; 2: a per-pixel colour image gathered beside the pixel record, no dependent gather)
+// build-time knob (MVS_NVCC_DEFS): resident CTAs the register allocation aims for.  Where the colour of the superpixel
+// under a projected sample comes from was a knob too; the two alternatives to the 16-byte colour record (a
+// per-superpixel cache of similarities in shared memory, a per-pixel colour image) were measured slower and are gone
+// (DESIGN 4.1).
 #ifndef PR_MINB
 #define PR_MINB 6
 #endif
-#ifndef PR_COL
-#define PR_COL 0
-#endif
-#ifndef PR_SIMC_SLOTS
-#define PR_SIMC_SLOTS 32
-#endif
-constexpr int PR_SIMC = PR_COL == 1 ? PR_SIMC_SLOTS : 0;   // slots of a superpixel's colour-similarity cache
-static_assert(PR_COL != 1 || (PR_SIMC >= 16 && (PR_SIMC & (PR_SIMC - 1)) == 0), "cache slots: a power of two, at least 16");
 
 struct PArgs {
     const float4 *map;        // [V][M][2]
@@ -63,9 +55,8 @@ struct PArgs {
     const float2 *flat;       // [V][M]
     const int *view_subset, *subset_num;
     const uint2 *pixd;        // [V][N] {label, input-plane disparity at the pixel} (k_pixel_plane)
-    const float4 *pixcol;     // [V][N] {L, a, b, 0} of the pixel's superpixel (k_pixel_colour; PR_COL 2)
     const float4 *spcol;      // [V][M] {L, a, b, 0} of every superpixel: half the bytes and half the cache lines of the
-                              //        32-byte centre records for the colour gather of the consistency walk (PR_COL 0)
+                              //        32-byte centre records for the colour gather of the consistency walk
     const float4 *plane_in;   // [V][M] {d,nx,ny,nz}
     const float2 *cost_in;    // [V][M] {sm,cs}
     float4 *plane_out;
@@ -81,13 +72,12 @@ struct PArgs {
     int nsmax;                // neighbour views per view at most (8 on a grid with neib_hor = neib_ver = 1)
     int hp;                   // planes whose smoothness products are staged at a time (phases G, H): PR_UB when their
                               // products fit the storage of the sample table, else 2
-    unsigned mw_magic;        // ceil(2^32 / mw): label -> approximate map row for the cache hash
-    unsigned long long *stats;   // optional counters {superpixels, candidates, unique planes, cache probes, cache misses}
+    unsigned long long *stats;   // optional work counters (mvs_frame_propagate_stats)
 };
 
 // shared-memory record of one superpixel (dynamic part sized by tmax / ncmax)
 struct SpLayout {
-    int meta, tab, cp, cc, cw, own, uniq, sres, stage, simc, total;
+    int meta, tab, cp, cc, cw, own, uniq, sres, stage, total;
 };
 
 // CTA layout: float4 viewt[nsmax] (one table: every superpixel of a CTA belongs to the same view), then one
@@ -105,7 +95,6 @@ __host__ __device__ inline SpLayout sp_layout(int tmax, int ncmax, int nsmax)
     L.sres = o;  o += 8 * PR_UB * nsmax;      // float2 per (plane, view): {term, flags}
     const int prod_bytes = 4 * sp_hp(tmax) * (tmax + 1), sdi_bytes = 16 * PR_UB * 9;
     L.stage = o; o += ((prod_bytes > sdi_bytes ? prod_bytes : sdi_bytes) + 15) & ~15;   // sdi (E,F) then prod (G,H)
-    L.simc = o;  o += 8 * PR_SIMC;            // {key, similarity} cache (PR_COL 1)
     L.cw = o;    o += 4 * ncmax;              // float acceptance weight (colour similarity to the source)
     L.own = o;   o += ncmax;                  // u8: slot whose costs this candidate takes
     L.uniq = o;  o += ncmax;                  // u8: slots of the unique planes, in order
@@ -196,11 +185,6 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     const float cx = ma.y, cy = ma.z, cL = ma.w, ca = mb.x, cb = mb.y;
     const float2 fl = a.flat[zM + sp];
     if (l8 == 0) *reinterpret_cast<float4 *>(sbase + L.meta) = make_float4(cL, ca, cb, 0.0f);
-    if (PIXD && PR_COL == 1) {   // empty cache: no key has view number 255
-        unsigned long long *simc = reinterpret_cast<unsigned long long *>(sbase + L.simc);
-#pragma unroll
-        for (int k = l8; k < PR_SIMC; k += 8) simc[k] = 0xFFFFFFFFull;
-    }
     const int ns = live ? a.subset_num[z] : 0;
     const int2 cz = a.cam[z];
     const int camx = cz.x, camy = cz.y;
@@ -354,18 +338,8 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                 if (PIXD) {
                     // Per sample ONE 8-byte gather: the label at the projected pixel and the disparity of that
                     // superpixel's input plane there (k_pixel_plane) -- no centre / plane gathers, no division.
-                    // The colour of that superpixel (for the similarity to the own colour) comes, by PR_COL, from its
-                    // centre record (a second, dependent gather), from that gather behind a per-superpixel cache of
-                    // similarities, or from a per-pixel colour image gathered beside the pixel record.
-#if PR_COL == 1
-                    // direct-mapped cache, key = view slot << 24 | q.  A hit returns the bits the computation gives.
-                    // Volatile 64-bit accesses: key and value must travel together -- split into two 32-bit loads, a
-                    // hit could pair its key with the value another lane stores in between.
-                    volatile unsigned long long *simc =
-                        reinterpret_cast<volatile unsigned long long *>(const_cast<unsigned char *>(ob) + L.simc);
-                    const uint32_t keyn = (uint32_t)n << 24;
-                    const int hn = (n & (PR_SIMC / 16 - 1)) << 4;
-#endif
+                    // The colour of that superpixel (for the similarity to the own colour) is a second, dependent
+                    // gather of its 16-byte colour record.
                     int n_vis = 0;
 #pragma unroll 1
                     for (int k0 = 0; k0 < 9; k0 += 3) {
@@ -391,15 +365,9 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                         uint2 pr[3];
 #pragma unroll
                         for (int j = 0; j < 3; ++j) pr[j] = __ldg(a.pixd + nbase + (uint32_t)pix[j]);
-#if PR_COL == 2
-                        float4 col[3];
-#pragma unroll
-                        for (int j = 0; j < 3; ++j) col[j] = __ldg(a.pixcol + nbase + (uint32_t)pix[j]);
-#elif PR_COL == 0
                         float4 col[3];
 #pragma unroll
                         for (int j = 0; j < 3; ++j) col[j] = __ldg(a.spcol + mbase + pr[j].x);
-#endif
 #pragma unroll
                         for (int j = 0; j < 3; ++j)
                             if (inb[j]) {
@@ -411,34 +379,8 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
                                     if (STATS) n_vis++;
                                 }
                                 else { if (diff != diff) visible += diff; ows += 1.0f; }
-                                float sim;
-#if PR_COL == 2
-                                {
-                                    const float cdiff = dist3(col[j].x, col[j].y, col[j].z, cL, ca, cb);
-                                    sim = expf_pinned<NP>(-cdiff * cdiff * a.gamma);
-                                }
-#elif PR_COL == 0
-                                {
-                                    const float cdiff = dist3(col[j].x, col[j].y, col[j].z, cL, ca, cb);
-                                    sim = expf_pinned<NP>(-cdiff * cdiff * a.gamma);
-                                }
-#else
-                                {
-                                    const uint32_t q = pr[j].x;
-                                    const uint32_t qy = __umulhi(q, a.mw_magic), qx = q - qy * (uint32_t)a.mw;
-                                    volatile unsigned long long *slot = simc + (hn | ((qy & 3u) << 2) | (qx & 3u));
-                                    const unsigned long long e = *slot;   // {key (low word), similarity bits}
-                                    if (STATS) atomicAdd(a.stats + 3, 1ull);
-                                    if ((uint32_t)e == (keyn | q)) sim = __uint_as_float((uint32_t)(e >> 32));
-                                    else {
-                                        if (STATS) atomicAdd(a.stats + 4, 1ull);
-                                        const Rec8 r = ld_rec8(a.map + 2 * (mbase + q));
-                                        const float cdiff = dist3(r.L, r.a, r.b, cL, ca, cb);
-                                        sim = expf_pinned<NP>(-cdiff * cdiff * a.gamma);
-                                        *slot = ((unsigned long long)__float_as_uint(sim) << 32) | (keyn | q);
-                                    }
-                                }
-#endif
+                                const float cdiff = dist3(col[j].x, col[j].y, col[j].z, cL, ca, cb);
+                                const float sim = expf_pinned<NP>(-cdiff * cdiff * a.gamma);
                                 visibility += sim;
                                 num += 1.0f;
                             }
@@ -649,10 +591,6 @@ __global__ void __launch_bounds__(PR_WARPS * 32, MINB) k_propagate(PArgs a)
     }
 }
 
-// what the consistency walk reads beside the frame's own arrays: 1 = the per-pixel record (k_pixel_plane of the
-// input state, every iteration), 2 = also the per-pixel colour image (k_pixel_colour, once per frame)
-int propagate_needs() { return PR_COL == 2 ? 2 : 1; }
-
 int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, int z0, int z1, cudaStream_t st,
                      unsigned long long *stats)
 {
@@ -660,7 +598,7 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     PArgs a;
     a.map = f.map; a.idx = f.idx; a.rep = f.rep; a.flat = f.flat;
     a.view_subset = f.view_subset; a.subset_num = f.subset_num;
-    a.pixd = f.pixd; a.pixcol = f.pixcol; a.spcol = f.spcol;
+    a.pixd = f.pixd; a.spcol = f.spcol;
     a.plane_in = f.plane[src]; a.cost_in = f.cost[src]; a.plane_out = f.plane[dst]; a.cost_out = f.cost[dst];
     a.V = f.V; a.W = f.W; a.H = f.H; a.mw = f.mw; a.mh = f.mh; a.N = f.N; a.M = f.M; a.cam = f.cam;
     a.gamma = r.gamma; a.alpha = r.alpha; a.bl_ratio = r.bl_ratio; a.fuse = r.fuse;
@@ -668,7 +606,6 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     a.kernel_step_size = r.kernel_step_size; a.iter = r.iter; a.z0 = z0;
     a.tmax = 8 + 4 * a.K;
     a.hp = sp_hp(a.tmax);
-    a.mw_magic = (unsigned)((0x100000000ULL + (unsigned)f.mw - 1) / (unsigned)f.mw);
     a.stats = stats;
     // candidate slots a superpixel can fill: 8 neighbours, the far neighbours whose offset fits the map
     // (same float -> int conversion as the kernel: truncation, saturating), 8 pairs
@@ -697,7 +634,7 @@ int launch_propagate(const FrameDev &f, const RefineArgs &r, int src, int dst, i
     const bool np = a.gamma >= 0.0f && a.alpha >= 0.0f;
     // the per-pixel record path needs f.pixd (k_pixel_plane of the SAME input state) and view slots below 255
     static const bool legacy = [] { const char *e = getenv("MVS_PROP_MODE"); return e && !strcmp(e, "legacy"); }();
-    const bool pixd = !legacy && f.pixd && a.nsmax < 255 && (PR_COL != 2 || f.pixcol) && (PR_COL != 0 || f.spcol);
+    const bool pixd = !legacy && f.pixd && f.spcol;
     // visible samples: |diff| < fuse and alpha >= 0, so the exp argument lies in (-fuse^2 alpha, 0]
     const bool sv = np && a.fuse >= 0.0f && (double)a.fuse * a.fuse * a.alpha < 0.34;
 #define PR_LAUNCH(U, B, P, X, S, SVV)                                                                            \

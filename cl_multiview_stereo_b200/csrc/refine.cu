@@ -356,27 +356,6 @@ int launch_spixl_colour(const FrameDev &f, int z0, int z1, cudaStream_t st)
     return 1;
 }
 
-// per-pixel colour of the pixel's superpixel (constant over the refinement; an experiment knob of k_propagate)
-__global__ void __launch_bounds__(256) k_pixel_colour(const float4 *__restrict__ map, const uint32_t *__restrict__ idx,
-                                                      float4 *__restrict__ pixcol, int W, int H, int N, int M, int z0)
-{
-    int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
-    int z = z0 + blockIdx.z;
-    if (x >= W || y >= H) return;
-    size_t pi = (size_t)z * N + (size_t)y * W + x;
-    uint32_t q = idx[pi];
-    float4 a = map[2 * ((size_t)z * M + q)], b = map[2 * ((size_t)z * M + q) + 1];
-    pixcol[pi] = make_float4(a.w, b.x, b.y, 0.0f);
-}
-
-int launch_pixel_colour(const FrameDev &f, int z0, int z1, cudaStream_t st)
-{
-    if (z1 <= z0) return 0;
-    dim3 b(32, 8), g((f.W + 31) / 32, (f.H + 7) / 8, z1 - z0);
-    k_pixel_colour<<<g, b, 0, st>>>(f.map, f.idx, f.pixcol, f.W, f.H, f.N, f.M, z0);
-    return 1;
-}
-
 int launch_pixel_plane(const FrameDev &f, int src, int z0, int z1, cudaStream_t st)
 {
     if (z1 <= z0) return 0;

@@ -158,7 +158,7 @@ int mvs_frame_flatness(mvs_frame *f);
 int mvs_frame_init_state(mvs_frame *f);
 int mvs_frame_propagate(mvs_frame *f, int iter);
 /* one propagate iteration with work counters (diagnostic): stats12 = {superpixels, candidate planes, unique planes
- * evaluated, similarity-cache probes, cache misses, (plane, view) items, items with samples inside the neighbour
+ * evaluated, 0, 0 (two retired counters), (plane, view) items, items with samples inside the neighbour
  * image, items with a visible sample, samples inside, visible samples, 0, 0} */
 int mvs_frame_propagate_stats(mvs_frame *f, int iter, unsigned long long *stats12);
 int mvs_frame_fusion(mvs_frame *f);
