@@ -397,45 +397,55 @@ def run_ours(args, rank, world, local_rank):
     stage = stage_split(frame, min(args.steps, 5))
 
     # ---- end to end through the public API with HOST buffers ---------------------------------
-    # two contexts/frames alternate so the copies of one frame overlap the kernels of the other
-    ctx2 = mvs.Context(local_rank)
-    frame2 = mvs.Frame(ctx2, s, W, H)
-    ctxs, frames = [ctx, ctx2], [frame, frame2]
+    # NCTX contexts/frames take turns, so that the copies of one frame overlap the kernels of another.  Two: with three
+    # (upload, kernels and download of three frames at once) the kernels of more frames interleave and evict each other
+    # from L2 -- measured 52.3 against 53.9 frames/s (MVS_E2E_CONTEXTS=3); the copies are 5 ms of an 18 ms frame anyway
+    NCTX = max(1, int(os.environ.get("MVS_E2E_CONTEXTS", "2")))
+    ctxs, frames = [ctx], [frame]
+    for _ in range(NCTX - 1):
+        ctxs.append(mvs.Context(local_rank))
+        frames.append(mvs.Frame(ctxs[-1], s, W, H))
     pin_in = mvs.PinnedBuffer(rgbx.shape, np.uint8)
     pin_in.array[...] = rgbx
-    pin_out = [mvs.PinnedBuffer((V, H, W), np.float32) for _ in range(2)]
+    pin_out = [mvs.PinnedBuffer((V, H, W), np.float32) for _ in range(NCTX)]
 
-    # The two streams interleave freely.  MVS_E2E_SERIAL=1 runs the two contexts' KERNELS one frame after the other
+    # The streams interleave freely.  MVS_E2E_SERIAL=1 runs the contexts' KERNELS one frame after the other
     # instead (mvs_ctx_wait_event on the other context's "run queued" event), so that only copies overlap kernels:
     # measured slower (19.10 against 18.91 ms per frame), the tails of one frame's kernels fill with the other's.
     serial = bool(os.environ.get("MVS_E2E_SERIAL"))
-    ran = [False, False]
+    ran = [False] * NCTX
 
     def e2e_step(i):
-        k = i & 1
+        k = i % NCTX
         ctxs[k].sync()                      # the previous frame on this context has fully landed
         frames[k].upload(mvs.BUF_RGBX, pin_in.array, sync=False)
-        if serial and ran[1 - k]:
-            ctxs[k].wait_event(ctxs[1 - k], 8)
+        if serial and NCTX > 1 and ran[(k - 1) % NCTX]:
+            ctxs[k].wait_event(ctxs[(k - 1) % NCTX], 8)
         frames[k].run()
         ctxs[k].event_record(8)
         ran[k] = True
         frames[k].download(mvs.BUF_DISP, out=pin_out[k].array, sync=False)
 
-    for i in range(max(args.warmup, 2)):
+    for i in range(max(args.warmup, NCTX)):
         e2e_step(i)
-    ctxs[0].sync(); ctxs[1].sync()
+    for c in ctxs:
+        c.sync()
     barrier()
     ctx.event_record(2)
     for i in range(args.steps):
         e2e_step(i)
-    ctxs[1].sync(); ctxs[0].sync()
+    for c in reversed(ctxs):
+        c.sync()
     ctx.event_record(3)
     ctx.sync()
     e2e_ms = max_over_ranks(ctx.event_elapsed_ms(2, 3)) / args.steps
-    checksum = float(np.nansum(pin_out[(args.steps - 1) & 1].array[0, ::64, ::64]))
+    checksum = float(np.nansum(pin_out[(args.steps - 1) % NCTX].array[0, ::64, ::64]))
     barrier()
-    frame2.close(); ctx2.close()
+    for f_, c_ in zip(frames[1:], ctxs[1:]):
+        f_.close(); c_.close()
+    for pb in pin_out:
+        pb.free()
+    pin_in.free()
 
     work = propagate_work(frame, s) if rank == 0 else None
 
@@ -640,39 +650,45 @@ def run_slic_batch(args, rank, world, local_rank):
     ms = max_over_ranks(ctx.event_elapsed_ms(0, 1)) / args.steps
     launches = ctx.launches - l0
     clocks = sampler.stop() if rank == 0 else None
-    # end to end: pinned host images in, labels + centres out, every step; two frames on two streams
-    # alternate so that the copies of one batch overlap the kernels of the other
-    ctx2 = mvs.Context(local_rank)
-    frame2 = mvs.Frame(ctx2, s, W, H)
-    ctxs, frames = [ctx, ctx2], [frame, frame2]
+    # end to end: pinned host images in, labels + centres out, every step; NCTX frames on as many streams take
+    # turns so that the upload of one batch, the kernels of another and the download of a third overlap: here copies
+    # and kernels take about 10 ms each per batch, and three contexts give 1104 images/s against 934 with two
+    NCTX = max(1, int(os.environ.get("MVS_E2E_CONTEXTS", "3")))
+    ctxs, frames = [ctx], [frame]
+    for _ in range(NCTX - 1):
+        ctxs.append(mvs.Context(local_rank))
+        frames.append(mvs.Frame(ctxs[-1], s, W, H))
     for f in frames:
         f.set_timing(False)
     pin_in = mvs.PinnedBuffer(imgs.shape, np.uint8)
     pin_in.array[...] = imgs
     mw, mh = mvs.map_size(W, H, s.spixl_size)
-    pin_idx = [mvs.PinnedBuffer((B, H, W), np.uint32) for _ in range(2)]
-    pin_map = [mvs.PinnedBuffer((B, mh, mw, 8), np.float32) for _ in range(2)]
+    pin_idx = [mvs.PinnedBuffer((B, H, W), np.uint32) for _ in range(NCTX)]
+    pin_map = [mvs.PinnedBuffer((B, mh, mw, 8), np.float32) for _ in range(NCTX)]
 
     def e2e_step(i):
-        k = i & 1
+        k = i % NCTX
         ctxs[k].sync()
         frames[k].upload(mvs.BUF_RGBX, pin_in.array, sync=False)
         frames[k].slic()
         frames[k].download(mvs.BUF_IDX, out=pin_idx[k].array, sync=False)
         frames[k].download(mvs.BUF_MAP, out=pin_map[k].array, sync=False)
 
-    for i in range(2):
+    for i in range(NCTX):
         e2e_step(i)
-    ctxs[0].sync(); ctxs[1].sync()
+    for c in ctxs:
+        c.sync()
     ctx.event_record(2)
     for i in range(args.steps):
         e2e_step(i)
-    ctxs[1].sync(); ctxs[0].sync()
+    for c in reversed(ctxs):
+        c.sync()
     ctx.event_record(3)
     ctx.sync()
     e2e_ms = max_over_ranks(ctx.event_elapsed_ms(2, 3)) / args.steps
-    pin_idx, pin_map = pin_idx[(args.steps - 1) & 1], pin_map[(args.steps - 1) & 1]
-    frame2.close(); ctx2.close()
+    pin_idx, pin_map = pin_idx[(args.steps - 1) % NCTX], pin_map[(args.steps - 1) % NCTX]
+    for f_, c_ in zip(frames[1:], ctxs[1:]):
+        f_.close(); c_.close()
     if rank == 0:
         peak = 6650.0
         try:
